@@ -1,0 +1,122 @@
+/* include/otter_b200.h — the drop-in boundary: a plain C ABI over the sm_100a CUDA hot path.
+ *
+ * What it replaces in the reference (paths relative to holstegelab/otter @ 2573c48e):
+ *   - the per-pair call chain  align_anreads (src/analignments.cpp:62-101)
+ *       -> wfa::WFAligner::alignEnd2End / alignEndsFree / getAlignmentScore
+ *          (include/WFA2-lib/bindings/cpp/WFAligner.cpp:75-137,208-210)
+ *       -> wavefront_align (include/WFA2-lib/wavefront/wavefront_align.c:465-479)
+ *     with the aligner otter constructs at src/assemble.cpp:49
+ *     (WFAlignerEdit(Score, MemoryMed), default WF-adaptive(10,50,1) heuristic);
+ *   - the pair loop of fill_dist_matrix (src/analignments.cpp:117-124) over a region's
+ *     valid reads, batched over thousands of regions per launch.
+ * Scores are the reference's integer scores (heuristic included), bit-exact.  The FP64
+ * dissimilarity is formed on the host with the reference's own expression
+ * (otter_b200/host/analignments_b200.cpp), never on the device.
+ *
+ * Conventions: plain pointers and sizes, no C++/torch types; every call returns an int status
+ * (OTGPU_OK == 0); nothing throws or exits; inputs are borrowed for the duration of the call and
+ * outputs are caller-allocated.  There is NO CPU fallback: without a CUDA device every compute
+ * entry point fails with OTGPU_ERR_NO_DEVICE.
+ *
+ * A context owns one CUDA stream, grow-only device buffers and pinned staging; it is not
+ * thread-safe (use one context per host thread / per device, as otter uses one aligner per
+ * thread, src/assemble.cpp:45-50).
+ */
+#ifndef OTTER_B200_H
+#define OTTER_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OTGPU_ABI_VERSION 1
+
+enum {
+  OTGPU_OK = 0,
+  OTGPU_ERR_ARGS = 1,      /* NULL / inconsistent arguments                                   */
+  OTGPU_ERR_NO_DEVICE = 2, /* no CUDA device / driver (there is no CPU fallback)              */
+  OTGPU_ERR_CUDA = 3,      /* a CUDA call or kernel failed; see otgpu_last_cuda_error         */
+  OTGPU_ERR_OOM = 4,       /* device or pinned-host allocation failed                         */
+  OTGPU_ERR_STATE = 5      /* call sequence error (e.g. align before upload)                  */
+};
+
+/* Score written for a pair whose wavefront became empty (WF_STATUS_UNFEASIBLE in
+ * include/WFA2-lib/wavefront/wavefront_aligner.h:53-57; unreachable for edit distance). */
+#define OTGPU_SCORE_UNFEASIBLE (-1)
+
+typedef struct otgpu_ctx otgpu_ctx;
+
+/* One alignment request.  pattern/text are read indices into the batch.
+ * pattern_begin_free < 0  => alignEnd2End(pattern, text)            (WFAligner.cpp:75-90)
+ * otherwise               => alignEndsFree(pattern, pbf, pef, text, tbf, tef) (:103-137). */
+typedef struct {
+  uint32_t pattern;
+  uint32_t text;
+  int32_t pattern_begin_free;
+  int32_t pattern_end_free;
+  int32_t text_begin_free;
+  int32_t text_end_free;
+} otgpu_pair;
+
+/* Per-launch work counters (diagnostics for the roofline / issue-bound argument). */
+typedef struct {
+  uint64_t n_pairs;
+  uint64_t n_pairs_8bit;   /* pairs routed to the byte-compare variant (non-ACGT present)  */
+  uint64_t n_pairs_wide;   /* pairs re-run with the wavefront in HBM (width > smem window) */
+  uint64_t kernel_launches;/* kernels launched by this context since creation              */
+} otgpu_stats;
+
+/* ---- lifecycle ------------------------------------------------------------------------- */
+int otgpu_abi_version(void);
+int otgpu_device_count(void); /* 0 when no device/driver; never fails */
+int otgpu_create(int device, otgpu_ctx** out);
+void otgpu_destroy(otgpu_ctx* ctx);
+const char* otgpu_strerror(int status);
+const char* otgpu_last_cuda_error(const otgpu_ctx* ctx);
+void* otgpu_stream(otgpu_ctx* ctx); /* the cudaStream_t every kernel of ctx is launched on */
+int otgpu_get_stats(const otgpu_ctx* ctx, otgpu_stats* out);
+
+/* Pinned host memory so callers can stage reads where H2D runs at full PCIe rate. */
+int otgpu_host_alloc(size_t bytes, void** out);
+void otgpu_host_free(void* p);
+
+/* ---- one-shot calls on HOST buffers (H2D + kernels + D2H inside the call) --------------- */
+
+/* Edit-distance scores for an explicit pair list.
+ * bases: concatenated read bytes (as std::string holds them; any byte values), read r occupies
+ * bases[read_off[r] .. read_off[r]+read_len[r]).  scores_out[n_pairs]. */
+int otgpu_edit_scores(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                      const uint64_t* read_off, const uint32_t* read_len, uint32_t n_reads,
+                      const otgpu_pair* pairs, uint64_t n_pairs, int32_t* scores_out);
+
+/* fill_dist_matrix for many regions at once (all listed reads valid and spanning).
+ * Region g owns reads [region_start[g], region_start[g+1]); its n(n-1)/2 scores are written in
+ * DistMatrix order (src/andistmat.cpp:15-21: (0,1),(0,2)..(n-2,n-1)) at
+ * scores_out + score_off[g].  For pair (i,j), i<j: pattern = the longer read, ties -> read i
+ * (src/analignments.cpp:67-70).  Equal strings score 0 like the reference's shortcut (:64). */
+int otgpu_region_edit_scores(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                             const uint64_t* read_off, const uint32_t* read_len,
+                             uint32_t n_reads, const uint32_t* region_start, uint32_t n_regions,
+                             const uint64_t* score_off, uint64_t n_scores, int32_t* scores_out);
+
+/* ---- split-phase calls (inputs stay resident in HBM between phases) ---------------------- */
+/* upload: async H2D of the batch on ctx's stream.  align: pack + pair expansion + alignment
+ * kernels, async on ctx's stream (may be called repeatedly on the resident batch).
+ * download: D2H of the scores + stream synchronize. */
+int otgpu_batch_upload_regions(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                               const uint64_t* read_off, const uint32_t* read_len,
+                               uint32_t n_reads, const uint32_t* region_start,
+                               uint32_t n_regions, const uint64_t* score_off, uint64_t n_scores);
+int otgpu_batch_upload_pairs(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                             const uint64_t* read_off, const uint32_t* read_len, uint32_t n_reads,
+                             const otgpu_pair* pairs, uint64_t n_pairs);
+int otgpu_batch_align(otgpu_ctx* ctx);
+int otgpu_batch_download(otgpu_ctx* ctx, int32_t* scores_out, uint64_t n_scores);
+int otgpu_synchronize(otgpu_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OTTER_B200_H */

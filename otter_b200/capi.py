@@ -1,0 +1,168 @@
+"""ctypes binding of include/otter_b200.h (one function per C entry point, nothing more)."""
+import ctypes as C
+import os
+
+import numpy as np
+
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libotter_b200.so")
+
+# Every symbol include/otter_b200.h declares; tests assert the library exports all of them.
+SYMBOLS = [
+    "otgpu_abi_version", "otgpu_device_count", "otgpu_create", "otgpu_destroy", "otgpu_strerror",
+    "otgpu_last_cuda_error", "otgpu_stream", "otgpu_get_stats", "otgpu_host_alloc",
+    "otgpu_host_free", "otgpu_edit_scores", "otgpu_region_edit_scores",
+    "otgpu_batch_upload_regions", "otgpu_batch_upload_pairs", "otgpu_batch_align",
+    "otgpu_batch_download", "otgpu_synchronize",
+]
+
+
+class OtgpuError(RuntimeError):
+    pass
+
+
+class Pair(C.Structure):
+    _fields_ = [("pattern", C.c_uint32), ("text", C.c_uint32), ("pattern_begin_free", C.c_int32),
+                ("pattern_end_free", C.c_int32), ("text_begin_free", C.c_int32),
+                ("text_end_free", C.c_int32)]
+
+
+PAIR_DTYPE = np.dtype([("pattern", "<u4"), ("text", "<u4"), ("pbf", "<i4"), ("pef", "<i4"),
+                       ("tbf", "<i4"), ("tef", "<i4")])
+
+
+class Stats(C.Structure):
+    _fields_ = [("n_pairs", C.c_uint64), ("n_pairs_8bit", C.c_uint64), ("n_pairs_wide", C.c_uint64),
+                ("kernel_launches", C.c_uint64)]
+
+
+_lib = None
+
+
+def lib():
+    """Load the CUDA library; fail loudly if it has not been built (no fallback exists)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise OtgpuError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; "
+                             "g.build()'` (nvcc, sm_100a). otter_b200 has no CPU fallback.")
+        l = C.CDLL(LIB_PATH)
+        vp, u64, u32, i32 = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int
+        l.otgpu_abi_version.restype = i32
+        l.otgpu_device_count.restype = i32
+        l.otgpu_create.argtypes = [i32, C.POINTER(vp)]
+        l.otgpu_destroy.argtypes = [vp]
+        l.otgpu_destroy.restype = None
+        l.otgpu_strerror.argtypes = [i32]
+        l.otgpu_strerror.restype = C.c_char_p
+        l.otgpu_last_cuda_error.argtypes = [vp]
+        l.otgpu_last_cuda_error.restype = C.c_char_p
+        l.otgpu_stream.argtypes = [vp]
+        l.otgpu_stream.restype = vp
+        l.otgpu_get_stats.argtypes = [vp, C.POINTER(Stats)]
+        l.otgpu_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
+        l.otgpu_host_free.argtypes = [vp]
+        l.otgpu_host_free.restype = None
+        l.otgpu_edit_scores.argtypes = [vp, vp, u64, vp, vp, u32, vp, u64, vp]
+        l.otgpu_region_edit_scores.argtypes = [vp, vp, u64, vp, vp, u32, vp, u32, vp, u64, vp]
+        l.otgpu_batch_upload_regions.argtypes = [vp, vp, u64, vp, vp, u32, vp, u32, vp, u64]
+        l.otgpu_batch_upload_pairs.argtypes = [vp, vp, u64, vp, vp, u32, vp, u64]
+        l.otgpu_batch_align.argtypes = [vp]
+        l.otgpu_batch_download.argtypes = [vp, vp, u64]
+        l.otgpu_synchronize.argtypes = [vp]
+        _lib = l
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None and a.size else None
+
+
+class PinnedArray:
+    """numpy view over otgpu_host_alloc memory."""
+
+    def __init__(self, shape, dtype):
+        self.dtype = np.dtype(dtype)
+        n = int(np.prod(shape)) * self.dtype.itemsize
+        self.ptr = C.c_void_p()
+        st = lib().otgpu_host_alloc(max(n, 1), C.byref(self.ptr))
+        if st != 0:
+            raise OtgpuError(lib().otgpu_strerror(st).decode())
+        buf = (C.c_uint8 * max(n, 1)).from_address(self.ptr.value)
+        self.array = np.frombuffer(buf, dtype=self.dtype, count=int(np.prod(shape))).reshape(shape)
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            lib().otgpu_host_free(self.ptr)
+            self.ptr = None
+
+
+class Context:
+    """Thin owner of an otgpu_ctx."""
+
+    def __init__(self, device=0):
+        self._l = lib()
+        self._h = C.c_void_p()
+        st = self._l.otgpu_create(device, C.byref(self._h))
+        if st != 0:
+            raise OtgpuError(self._l.otgpu_strerror(st).decode())
+
+    def close(self):
+        if self._h:
+            self._l.otgpu_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _ck(self, st):
+        if st != 0:
+            raise OtgpuError(f"{self._l.otgpu_strerror(st).decode()}: "
+                             f"{self._l.otgpu_last_cuda_error(self._h).decode()}")
+
+    @property
+    def stream(self):
+        return self._l.otgpu_stream(self._h)
+
+    def stats(self):
+        s = Stats()
+        self._ck(self._l.otgpu_get_stats(self._h, C.byref(s)))
+        return dict(n_pairs=s.n_pairs, n_pairs_8bit=s.n_pairs_8bit, n_pairs_wide=s.n_pairs_wide,
+                    kernel_launches=s.kernel_launches)
+
+    def edit_scores(self, bases, off, lens, pairs):
+        pairs = np.ascontiguousarray(pairs, dtype=PAIR_DTYPE)
+        out = np.empty(len(pairs), dtype=np.int32)
+        self._ck(self._l.otgpu_edit_scores(self._h, _p(bases), bases.size, _p(off), _p(lens),
+                                           len(lens), _p(pairs), len(pairs), _p(out)))
+        return out
+
+    def region_edit_scores(self, bases, off, lens, region_start, score_off, n_scores):
+        out = np.empty(n_scores, dtype=np.int32)
+        self._ck(self._l.otgpu_region_edit_scores(self._h, _p(bases), bases.size, _p(off), _p(lens),
+                                                  len(lens), _p(region_start), len(region_start) - 1,
+                                                  _p(score_off), n_scores, _p(out)))
+        return out
+
+    def upload_regions(self, bases, off, lens, region_start, score_off, n_scores):
+        self._ck(self._l.otgpu_batch_upload_regions(self._h, _p(bases), bases.size, _p(off),
+                                                    _p(lens), len(lens), _p(region_start),
+                                                    len(region_start) - 1, _p(score_off), n_scores))
+
+    def upload_pairs(self, bases, off, lens, pairs):
+        pairs = np.ascontiguousarray(pairs, dtype=PAIR_DTYPE)
+        self._ck(self._l.otgpu_batch_upload_pairs(self._h, _p(bases), bases.size, _p(off), _p(lens),
+                                                  len(lens), _p(pairs), len(pairs)))
+
+    def align(self):
+        self._ck(self._l.otgpu_batch_align(self._h))
+
+    def download(self, out):
+        self._ck(self._l.otgpu_batch_download(self._h, _p(out), out.size))
+        return out
+
+    def synchronize(self):
+        self._ck(self._l.otgpu_synchronize(self._h))

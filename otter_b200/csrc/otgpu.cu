@@ -1,0 +1,518 @@
+// otter_b200/csrc/otgpu.cu — C ABI of include/otter_b200.h + batch kernels (sm_100a).
+//
+// Pipeline of one batch on the context's stream (no host sync until download):
+//   H2D(raw bases, read table, region table | pair list)
+//   -> k_pack_reads      raw bytes -> 2-bit words, flags reads holding a non-ACGT byte
+//   -> k_expand_regions  region table -> explicit (pattern,text) list in DistMatrix order,
+//                        pattern = longer read (reference src/analignments.cpp:67-70)
+//   -> k_align<false>    persistent warps, one pair per warp, wavefront ring in shared memory
+//   -> k_align<true>     the few pairs whose live width outgrew the ring, wavefront in HBM
+//   D2H(int32 scores)
+// There is no CPU path: every entry point needs a CUDA device.
+#include "../../include/otter_b200.h"
+#include "wfa_edit.cuh"
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+
+using namespace otgpu;
+
+namespace {
+
+constexpr int kRingCap = 512;      // int32 slots per warp in shared memory (live width <= 509)
+constexpr int kWarpsPerCta = 8;
+constexpr int kCtaThreads = kWarpsPerCta * 32;
+constexpr uint32_t kEmptySlot = 0xffffffffu;
+
+struct DevBatch {
+  const uint8_t* bases;      // raw bytes (+16 B slack)
+  const uint64_t* read_off;  // byte offset of each read in bases
+  const uint32_t* read_len;
+  const uint64_t* pk_off;    // word offset of each read in packed
+  const uint32_t* packed;    // 2-bit words, 16 bases per word
+  uint32_t* read_flag;       // bit0: read holds a byte outside {A,C,G,T}
+  const otgpu_pair* pairs;
+  int32_t* scores;
+  uint64_t n_pairs;
+  uint32_t n_reads;
+};
+
+// counters[0] main queue, [1] overflow count, [2] wide queue, [3] 8-bit pairs
+struct Counters { unsigned long long v[4]; };
+
+__global__ void __launch_bounds__(128) k_pack_reads(DevBatch b, uint32_t* __restrict__ packed) {
+  const uint32_t r = blockIdx.x;
+  const uint32_t len = b.read_len[r];
+  const uint8_t* __restrict__ src = b.bases + b.read_off[r];
+  uint32_t* __restrict__ dst = packed + b.pk_off[r];
+  const uint32_t nwords = (len + 15) / 16 + 2;  // + guard words the window loads may touch
+  bool bad = false;
+  for (uint32_t w = threadIdx.x; w < nwords; w += blockDim.x) {
+    uint32_t word = 0;
+    const uint32_t p0 = w * 16;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const uint32_t p = p0 + i;
+      if (p < len) {
+        const uint32_t c = src[p];
+        bad |= !(c == 'A' || c == 'C' || c == 'G' || c == 'T');
+        word |= ((c >> 1) & 3u) << (2 * i);
+      }
+    }
+    dst[w] = word;
+  }
+  if (bad) atomicOr(&b.read_flag[r], 1u);
+}
+
+__global__ void __launch_bounds__(128) k_expand_regions(const uint32_t* __restrict__ region_start,
+                                                        const uint64_t* __restrict__ score_off,
+                                                        const uint32_t* __restrict__ read_len,
+                                                        otgpu_pair* __restrict__ pairs) {
+  const uint32_t g = blockIdx.x;
+  const uint32_t r0 = region_start[g];
+  const uint32_t n = region_start[g + 1] - r0;
+  otgpu_pair* out = pairs + score_off[g];
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  for (uint32_t i = warp; i + 1 < n; i += nw) {
+    const uint64_t row = (uint64_t)i * (2ull * n - i - 1) / 2;  // src/andistmat.cpp:20
+    const uint32_t li = read_len[r0 + i];
+    for (uint32_t j = i + 1 + lane; j < n; j += 32) {
+      const uint32_t lj = read_len[r0 + j];
+      otgpu_pair p;
+      const bool x_is_smallest = li < lj;  // src/analignments.cpp:67
+      p.pattern = x_is_smallest ? r0 + j : r0 + i;
+      p.text = x_is_smallest ? r0 + i : r0 + j;
+      p.pattern_begin_free = -1;
+      p.pattern_end_free = p.text_begin_free = p.text_end_free = 0;
+      out[row + (j - i - 1)] = p;
+    }
+  }
+}
+
+__device__ __forceinline__ SeqView view2(const DevBatch& b, uint32_t r) {
+  return SeqView{b.packed + b.pk_off[r], 0};
+}
+__device__ __forceinline__ SeqView view8(const DevBatch& b, uint32_t r) {
+  const uint64_t o = b.read_off[r];
+  return SeqView{reinterpret_cast<const uint32_t*>(b.bases + (o & ~3ull)), (int)(o & 3ull)};
+}
+
+template <bool WIDE>
+__global__ void __launch_bounds__(kCtaThreads)
+k_align(DevBatch b, Counters* __restrict__ ctr, uint32_t* __restrict__ ovf_list,
+        int32_t* __restrict__ wide_ws, int wide_cap) {
+  __shared__ int32_t ring_smem[WIDE ? 1 : kWarpsPerCta * kRingCap];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int32_t* ring;
+  int mask;
+  if (WIDE) {
+    ring = wide_ws + (size_t)(blockIdx.x * kWarpsPerCta + warp) * wide_cap;
+    mask = wide_cap - 1;
+  } else {
+    ring = ring_smem + warp * kRingCap;
+    mask = kRingCap - 1;
+  }
+  const unsigned long long limit = WIDE ? ctr->v[1] : b.n_pairs;
+  for (;;) {
+    unsigned long long q = 0;
+    if (lane == 0) q = atomicAdd(&ctr->v[WIDE ? 2 : 0], 1ull);
+    q = __shfl_sync(kFull, q, 0);
+    if (q >= limit) break;
+    const uint64_t idx = WIDE ? ovf_list[q] : q;
+    const otgpu_pair pr = b.pairs[idx];
+    if (pr.pattern == kEmptySlot) {
+      if (lane == 0) b.scores[idx] = 0;
+      continue;
+    }
+    EditJob J;
+    J.plen = (int)b.read_len[pr.pattern];
+    J.tlen = (int)b.read_len[pr.text];
+    J.pb = pr.pattern_begin_free; J.pe = pr.pattern_end_free;
+    J.tb = pr.text_begin_free;    J.te = pr.text_end_free;
+    const bool bytes = ((b.read_flag[pr.pattern] | b.read_flag[pr.text]) & 1u) != 0;
+    int score;
+    if (bytes) {
+      J.P = view8(b, pr.pattern); J.T = view8(b, pr.text);
+      score = wfa_edit_pair<8, WIDE>(ring, mask, J, lane);
+      if (!WIDE && lane == 0) atomicAdd(&ctr->v[3], 1ull);
+    } else {
+      J.P = view2(b, pr.pattern); J.T = view2(b, pr.text);
+      score = wfa_edit_pair<2, WIDE>(ring, mask, J, lane);
+    }
+    __syncwarp();
+    if (lane == 0) {
+      if (!WIDE && score == kScoreOverflow) {
+        const unsigned long long pos = atomicAdd(&ctr->v[1], 1ull);
+        ovf_list[pos] = (uint32_t)idx;
+      } else {
+        b.scores[idx] = score;
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+};
+
+}  // namespace
+
+struct otgpu_ctx {
+  int device = 0;
+  int n_sm = 0;
+  cudaStream_t stream = nullptr;
+  char err[256] = {0};
+  DevBuf bases, read_off, read_len, pk_off, read_flag, packed, region_start, score_off, pairs,
+      scores, ovf_list, counters, wide_ws;
+  void* h_pk_off = nullptr;  // pinned
+  size_t h_pk_off_cap = 0;
+  void* h_counters = nullptr;  // pinned, 4 x u64
+  // resident batch
+  bool resident = false, by_regions = false;
+  uint64_t n_bases = 0, n_pairs = 0, n_packed_words = 0;
+  uint32_t n_reads = 0, n_regions = 0, max_len = 0;
+  int grid_main = 0, grid_wide = 0, wide_cap = 0;
+  otgpu_stats stats = {0, 0, 0, 0};
+};
+
+namespace {
+
+int fail_cuda(otgpu_ctx* c, cudaError_t e, const char* what) {
+  snprintf(c->err, sizeof(c->err), "%s: %s", what, cudaGetErrorString(e));
+  return e == cudaErrorMemoryAllocation ? OTGPU_ERR_OOM : OTGPU_ERR_CUDA;
+}
+#define CK(call)                                              \
+  do {                                                        \
+    cudaError_t e_ = (call);                                  \
+    if (e_ != cudaSuccess) return fail_cuda(ctx, e_, #call);  \
+  } while (0)
+
+int reserve(otgpu_ctx* ctx, DevBuf& b, size_t bytes) {
+  if (bytes <= b.cap) return OTGPU_OK;
+  if (b.p) CK(cudaFree(b.p));
+  b.p = nullptr;
+  b.cap = 0;
+  size_t want = bytes + bytes / 8 + 256;
+  CK(cudaMalloc(&b.p, want));
+  b.cap = want;
+  return OTGPU_OK;
+}
+#define RS(buf, bytes)                              \
+  do {                                              \
+    int s_ = reserve(ctx, ctx->buf, (bytes));       \
+    if (s_ != OTGPU_OK) return s_;                  \
+  } while (0)
+
+int next_pow2(int x) {
+  int p = 1;
+  while (p < x) p <<= 1;
+  return p;
+}
+
+// Shared front half of both upload flavours: reads + packed layout.
+int upload_reads(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const uint64_t* read_off,
+                 const uint32_t* read_len, uint32_t n_reads) {
+  if (!ctx || (!bases && n_bases) || !read_off || !read_len) return OTGPU_ERR_ARGS;
+  CK(cudaSetDevice(ctx->device));
+  // the previous batch (device buffers, pinned staging) must be finished before it is replaced
+  CK(cudaStreamSynchronize(ctx->stream));
+  if ((size_t)n_reads * 8 > ctx->h_pk_off_cap) {
+    if (ctx->h_pk_off) cudaFreeHost(ctx->h_pk_off);
+    ctx->h_pk_off = nullptr;
+    ctx->h_pk_off_cap = 0;
+    size_t want = (size_t)n_reads * 8 + (size_t)n_reads + 4096;
+    CK(cudaMallocHost(&ctx->h_pk_off, want));
+    ctx->h_pk_off_cap = want;
+  }
+  uint64_t* pk = static_cast<uint64_t*>(ctx->h_pk_off);
+  uint64_t words = 0;
+  uint32_t max_len = 0;
+  for (uint32_t r = 0; r < n_reads; ++r) {
+    if (read_off[r] + read_len[r] > n_bases) {
+      snprintf(ctx->err, sizeof(ctx->err), "read %u exceeds the bases buffer", r);
+      return OTGPU_ERR_ARGS;
+    }
+    pk[r] = words;
+    words += (((uint64_t)read_len[r] + 15) / 16 + 2 + 3) & ~3ull;  // 16 B aligned, >= 2 guards
+    if (read_len[r] > max_len) max_len = read_len[r];
+  }
+  RS(bases, n_bases + 16);
+  RS(read_off, (size_t)n_reads * 8 + 8);
+  RS(read_len, (size_t)n_reads * 4 + 4);
+  RS(pk_off, (size_t)n_reads * 8 + 8);
+  RS(read_flag, (size_t)n_reads * 4 + 4);
+  RS(packed, (words + 4) * 4);
+  RS(counters, sizeof(Counters));
+  if (n_bases) CK(cudaMemcpyAsync(ctx->bases.p, bases, n_bases, cudaMemcpyHostToDevice, ctx->stream));
+  if (n_reads) {
+    CK(cudaMemcpyAsync(ctx->read_off.p, read_off, (size_t)n_reads * 8, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->read_len.p, read_len, (size_t)n_reads * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->pk_off.p, pk, (size_t)n_reads * 8, cudaMemcpyHostToDevice, ctx->stream));
+  }
+  ctx->n_bases = n_bases;
+  ctx->n_reads = n_reads;
+  ctx->n_packed_words = words;
+  ctx->max_len = max_len;
+  return OTGPU_OK;
+}
+
+int size_launch(otgpu_ctx* ctx) {
+  if (ctx->grid_main == 0) {
+    int per_sm = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_align<false>, kCtaThreads, 0));
+    if (per_sm < 1) per_sm = 1;
+    ctx->grid_main = ctx->n_sm * per_sm;
+  }
+  // wide fallback: ring must hold every diagonal of the longest possible pair
+  const int need = next_pow2(2 * (int)ctx->max_len + 16);
+  int grid_wide = ctx->n_sm * 2;
+  const size_t budget = (size_t)4 << 30;
+  while (grid_wide > 1 && (size_t)grid_wide * kWarpsPerCta * need * 4 > budget) grid_wide /= 2;
+  ctx->wide_cap = need;
+  ctx->grid_wide = grid_wide;
+  RS(wide_ws, (size_t)grid_wide * kWarpsPerCta * need * 4);
+  return OTGPU_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int otgpu_abi_version(void) { return OTGPU_ABI_VERSION; }
+
+int otgpu_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+const char* otgpu_strerror(int status) {
+  switch (status) {
+    case OTGPU_OK: return "ok";
+    case OTGPU_ERR_ARGS: return "invalid arguments";
+    case OTGPU_ERR_NO_DEVICE: return "no CUDA device (otter_b200 has no CPU fallback)";
+    case OTGPU_ERR_CUDA: return "CUDA error";
+    case OTGPU_ERR_OOM: return "out of memory";
+    case OTGPU_ERR_STATE: return "call sequence error";
+    default: return "unknown status";
+  }
+}
+
+int otgpu_create(int device, otgpu_ctx** out) {
+  if (!out) return OTGPU_ERR_ARGS;
+  *out = nullptr;
+  if (device < 0 || device >= otgpu_device_count()) return OTGPU_ERR_NO_DEVICE;
+  otgpu_ctx* ctx = new (std::nothrow) otgpu_ctx();
+  if (!ctx) return OTGPU_ERR_OOM;
+  ctx->device = device;
+  cudaError_t e = cudaSetDevice(device);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&ctx->n_sm, cudaDevAttrMultiProcessorCount, device);
+  if (e == cudaSuccess) e = cudaMallocHost(&ctx->h_counters, sizeof(Counters));
+  if (e != cudaSuccess) {
+    delete ctx;
+    return OTGPU_ERR_CUDA;
+  }
+  *out = ctx;
+  return OTGPU_OK;
+}
+
+void otgpu_destroy(otgpu_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  DevBuf* bufs[] = {&ctx->bases, &ctx->read_off, &ctx->read_len, &ctx->pk_off, &ctx->read_flag,
+                    &ctx->packed, &ctx->region_start, &ctx->score_off, &ctx->pairs, &ctx->scores,
+                    &ctx->ovf_list, &ctx->counters, &ctx->wide_ws};
+  for (DevBuf* b : bufs)
+    if (b->p) cudaFree(b->p);
+  if (ctx->h_pk_off) cudaFreeHost(ctx->h_pk_off);
+  if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+const char* otgpu_last_cuda_error(const otgpu_ctx* ctx) { return ctx ? ctx->err : ""; }
+void* otgpu_stream(otgpu_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+int otgpu_get_stats(const otgpu_ctx* ctx, otgpu_stats* out) {
+  if (!ctx || !out) return OTGPU_ERR_ARGS;
+  *out = ctx->stats;
+  return OTGPU_OK;
+}
+
+int otgpu_host_alloc(size_t bytes, void** out) {
+  if (!out) return OTGPU_ERR_ARGS;
+  *out = nullptr;
+  if (otgpu_device_count() == 0) return OTGPU_ERR_NO_DEVICE;
+  cudaError_t e = cudaMallocHost(out, bytes ? bytes : 1);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return OTGPU_ERR_OOM;
+  }
+  return OTGPU_OK;
+}
+void otgpu_host_free(void* p) {
+  if (p) cudaFreeHost(p);
+}
+
+int otgpu_batch_upload_regions(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                               const uint64_t* read_off, const uint32_t* read_len,
+                               uint32_t n_reads, const uint32_t* region_start,
+                               uint32_t n_regions, const uint64_t* score_off, uint64_t n_scores) {
+  if (!ctx || !region_start || !score_off) return OTGPU_ERR_ARGS;
+  ctx->resident = false;
+  for (uint32_t g = 0; g < n_regions; ++g) {
+    if (region_start[g + 1] < region_start[g] || region_start[g + 1] > n_reads) return OTGPU_ERR_ARGS;
+    const uint64_t n = region_start[g + 1] - region_start[g];
+    if (score_off[g] + n * (n - (n ? 1 : 0)) / 2 > n_scores) return OTGPU_ERR_ARGS;
+  }
+  if (n_scores >= 0xffffffffull) return OTGPU_ERR_ARGS;  // overflow list holds 32-bit slots
+  int s = upload_reads(ctx, bases, n_bases, read_off, read_len, n_reads);
+  if (s != OTGPU_OK) return s;
+  RS(region_start, (size_t)(n_regions + 1) * 4);
+  RS(score_off, (size_t)n_regions * 8 + 8);
+  RS(pairs, (size_t)n_scores * sizeof(otgpu_pair) + 32);
+  RS(scores, (size_t)n_scores * 4 + 4);
+  RS(ovf_list, (size_t)n_scores * 4 + 4);
+  CK(cudaMemcpyAsync(ctx->region_start.p, region_start, (size_t)(n_regions + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
+  if (n_regions)
+    CK(cudaMemcpyAsync(ctx->score_off.p, score_off, (size_t)n_regions * 8, cudaMemcpyHostToDevice, ctx->stream));
+  ctx->n_regions = n_regions;
+  ctx->n_pairs = n_scores;
+  ctx->by_regions = true;
+  s = size_launch(ctx);
+  if (s != OTGPU_OK) return s;
+  ctx->resident = true;
+  return OTGPU_OK;
+}
+
+int otgpu_batch_upload_pairs(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                             const uint64_t* read_off, const uint32_t* read_len, uint32_t n_reads,
+                             const otgpu_pair* pairs, uint64_t n_pairs) {
+  if (!ctx || (!pairs && n_pairs)) return OTGPU_ERR_ARGS;
+  ctx->resident = false;
+  if (n_pairs >= 0xffffffffull) return OTGPU_ERR_ARGS;
+  for (uint64_t i = 0; i < n_pairs; ++i) {
+    const otgpu_pair& p = pairs[i];
+    if (p.pattern >= n_reads || p.text >= n_reads) return OTGPU_ERR_ARGS;
+    if (p.pattern_begin_free >= 0) {
+      // wavefront_check_endsfree_form (wavefront_align.c:40-61) would exit(1) on these
+      if (p.pattern_end_free < 0 || p.text_begin_free < 0 || p.text_end_free < 0 ||
+          (uint32_t)p.pattern_begin_free > read_len[p.pattern] ||
+          (uint32_t)p.pattern_end_free > read_len[p.pattern] ||
+          (uint32_t)p.text_begin_free > read_len[p.text] ||
+          (uint32_t)p.text_end_free > read_len[p.text])
+        return OTGPU_ERR_ARGS;
+    }
+  }
+  int s = upload_reads(ctx, bases, n_bases, read_off, read_len, n_reads);
+  if (s != OTGPU_OK) return s;
+  RS(pairs, (size_t)n_pairs * sizeof(otgpu_pair) + 32);
+  RS(scores, (size_t)n_pairs * 4 + 4);
+  RS(ovf_list, (size_t)n_pairs * 4 + 4);
+  if (n_pairs)
+    CK(cudaMemcpyAsync(ctx->pairs.p, pairs, (size_t)n_pairs * sizeof(otgpu_pair), cudaMemcpyHostToDevice, ctx->stream));
+  ctx->n_pairs = n_pairs;
+  ctx->n_regions = 0;
+  ctx->by_regions = false;
+  s = size_launch(ctx);
+  if (s != OTGPU_OK) return s;
+  ctx->resident = true;
+  return OTGPU_OK;
+}
+
+int otgpu_batch_align(otgpu_ctx* ctx) {
+  if (!ctx) return OTGPU_ERR_ARGS;
+  if (!ctx->resident) return OTGPU_ERR_STATE;
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  DevBatch b;
+  b.bases = static_cast<const uint8_t*>(ctx->bases.p);
+  b.read_off = static_cast<const uint64_t*>(ctx->read_off.p);
+  b.read_len = static_cast<const uint32_t*>(ctx->read_len.p);
+  b.pk_off = static_cast<const uint64_t*>(ctx->pk_off.p);
+  b.packed = static_cast<const uint32_t*>(ctx->packed.p);
+  b.read_flag = static_cast<uint32_t*>(ctx->read_flag.p);
+  b.pairs = static_cast<const otgpu_pair*>(ctx->pairs.p);
+  b.scores = static_cast<int32_t*>(ctx->scores.p);
+  b.n_pairs = ctx->n_pairs;
+  b.n_reads = ctx->n_reads;
+  CK(cudaMemsetAsync(ctx->counters.p, 0, sizeof(Counters), st));
+  if (ctx->n_reads) {
+    CK(cudaMemsetAsync(ctx->read_flag.p, 0, (size_t)ctx->n_reads * 4, st));
+    k_pack_reads<<<ctx->n_reads, 128, 0, st>>>(b, static_cast<uint32_t*>(ctx->packed.p));
+    ctx->stats.kernel_launches++;
+  }
+  if (ctx->by_regions && ctx->n_pairs) {
+    CK(cudaMemsetAsync(ctx->pairs.p, 0xff, (size_t)ctx->n_pairs * sizeof(otgpu_pair), st));
+    if (ctx->n_regions) {
+      k_expand_regions<<<ctx->n_regions, 128, 0, st>>>(
+          static_cast<const uint32_t*>(ctx->region_start.p),
+          static_cast<const uint64_t*>(ctx->score_off.p), b.read_len,
+          static_cast<otgpu_pair*>(ctx->pairs.p));
+      ctx->stats.kernel_launches++;
+    }
+  }
+  if (ctx->n_pairs) {
+    Counters* ctr = static_cast<Counters*>(ctx->counters.p);
+    uint32_t* ovf = static_cast<uint32_t*>(ctx->ovf_list.p);
+    k_align<false><<<ctx->grid_main, kCtaThreads, 0, st>>>(b, ctr, ovf, nullptr, 0);
+    k_align<true><<<ctx->grid_wide, kCtaThreads, 0, st>>>(
+        b, ctr, ovf, static_cast<int32_t*>(ctx->wide_ws.p), ctx->wide_cap);
+    ctx->stats.kernel_launches += 2;
+  }
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(ctx->h_counters, ctx->counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+  return OTGPU_OK;
+}
+
+int otgpu_synchronize(otgpu_ctx* ctx) {
+  if (!ctx) return OTGPU_ERR_ARGS;
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return OTGPU_OK;
+}
+
+int otgpu_batch_download(otgpu_ctx* ctx, int32_t* scores_out, uint64_t n_scores) {
+  if (!ctx || (!scores_out && n_scores)) return OTGPU_ERR_ARGS;
+  if (!ctx->resident || n_scores != ctx->n_pairs) return OTGPU_ERR_STATE;
+  CK(cudaSetDevice(ctx->device));
+  if (n_scores)
+    CK(cudaMemcpyAsync(scores_out, ctx->scores.p, (size_t)n_scores * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  const Counters* hc = static_cast<const Counters*>(ctx->h_counters);
+  ctx->stats.n_pairs = ctx->n_pairs;
+  ctx->stats.n_pairs_wide = hc->v[1];
+  ctx->stats.n_pairs_8bit = hc->v[3];
+  return OTGPU_OK;
+}
+
+int otgpu_edit_scores(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                      const uint64_t* read_off, const uint32_t* read_len, uint32_t n_reads,
+                      const otgpu_pair* pairs, uint64_t n_pairs, int32_t* scores_out) {
+  int s = otgpu_batch_upload_pairs(ctx, bases, n_bases, read_off, read_len, n_reads, pairs, n_pairs);
+  if (s == OTGPU_OK) s = otgpu_batch_align(ctx);
+  if (s == OTGPU_OK) s = otgpu_batch_download(ctx, scores_out, n_pairs);
+  return s;
+}
+
+int otgpu_region_edit_scores(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                             const uint64_t* read_off, const uint32_t* read_len,
+                             uint32_t n_reads, const uint32_t* region_start, uint32_t n_regions,
+                             const uint64_t* score_off, uint64_t n_scores, int32_t* scores_out) {
+  int s = otgpu_batch_upload_regions(ctx, bases, n_bases, read_off, read_len, n_reads,
+                                     region_start, n_regions, score_off, n_scores);
+  if (s == OTGPU_OK) s = otgpu_batch_align(ctx);
+  if (s == OTGPU_OK) s = otgpu_batch_download(ctx, scores_out, n_scores);
+  return s;
+}
+
+}  // extern "C"
