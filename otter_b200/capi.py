@@ -12,7 +12,7 @@ SYMBOLS = [
     "otgpu_last_cuda_error", "otgpu_stream", "otgpu_get_stats", "otgpu_host_alloc",
     "otgpu_host_free", "otgpu_edit_scores", "otgpu_region_edit_scores",
     "otgpu_batch_upload_regions", "otgpu_batch_upload_pairs", "otgpu_batch_align",
-    "otgpu_batch_download", "otgpu_synchronize",
+    "otgpu_batch_download", "otgpu_synchronize", "otgpu_last_align_ms",
 ]
 
 
@@ -69,6 +69,7 @@ def lib():
         l.otgpu_batch_align.argtypes = [vp]
         l.otgpu_batch_download.argtypes = [vp, vp, u64]
         l.otgpu_synchronize.argtypes = [vp]
+        l.otgpu_last_align_ms.argtypes = [vp, C.POINTER(C.c_float * 4)]
         _lib = l
     return _lib
 
@@ -163,6 +164,11 @@ class Context:
     def download(self, out):
         self._ck(self._l.otgpu_batch_download(self._h, _p(out), out.size))
         return out
+
+    def last_align_ms(self):
+        ms = (C.c_float * 4)()
+        self._ck(self._l.otgpu_last_align_ms(self._h, C.byref(ms)))
+        return dict(pack=ms[0], expand=ms[1], align=ms[2], wide=ms[3])
 
     def synchronize(self):
         self._ck(self._l.otgpu_synchronize(self._h))

@@ -177,6 +177,8 @@ struct otgpu_ctx {
   uint32_t n_reads = 0, n_regions = 0, max_len = 0;
   int grid_main = 0, grid_wide = 0, wide_cap = 0;
   otgpu_stats stats = {0, 0, 0, 0};
+  cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // pack|expand|align|wide|end
+  bool timed = false;
 };
 
 namespace {
@@ -316,6 +318,7 @@ int otgpu_create(int device, otgpu_ctx** out) {
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&ctx->n_sm, cudaDevAttrMultiProcessorCount, device);
   if (e == cudaSuccess) e = cudaMallocHost(&ctx->h_counters, sizeof(Counters));
+  for (int i = 0; i < 5 && e == cudaSuccess; ++i) e = cudaEventCreate(&ctx->ev[i]);
   if (e != cudaSuccess) {
     delete ctx;
     return OTGPU_ERR_CUDA;
@@ -335,6 +338,8 @@ void otgpu_destroy(otgpu_ctx* ctx) {
     if (b->p) cudaFree(b->p);
   if (ctx->h_pk_off) cudaFreeHost(ctx->h_pk_off);
   if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
+  for (cudaEvent_t e : ctx->ev)
+    if (e) cudaEventDestroy(e);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -446,11 +451,13 @@ int otgpu_batch_align(otgpu_ctx* ctx) {
   b.n_pairs = ctx->n_pairs;
   b.n_reads = ctx->n_reads;
   CK(cudaMemsetAsync(ctx->counters.p, 0, sizeof(Counters), st));
+  CK(cudaEventRecord(ctx->ev[0], st));
   if (ctx->n_reads) {
     CK(cudaMemsetAsync(ctx->read_flag.p, 0, (size_t)ctx->n_reads * 4, st));
     k_pack_reads<<<ctx->n_reads, 128, 0, st>>>(b, static_cast<uint32_t*>(ctx->packed.p));
     ctx->stats.kernel_launches++;
   }
+  CK(cudaEventRecord(ctx->ev[1], st));
   if (ctx->by_regions && ctx->n_pairs) {
     CK(cudaMemsetAsync(ctx->pairs.p, 0xff, (size_t)ctx->n_pairs * sizeof(otgpu_pair), st));
     if (ctx->n_regions) {
@@ -461,16 +468,31 @@ int otgpu_batch_align(otgpu_ctx* ctx) {
       ctx->stats.kernel_launches++;
     }
   }
+  CK(cudaEventRecord(ctx->ev[2], st));
   if (ctx->n_pairs) {
     Counters* ctr = static_cast<Counters*>(ctx->counters.p);
     uint32_t* ovf = static_cast<uint32_t*>(ctx->ovf_list.p);
     k_align<false><<<ctx->grid_main, kCtaThreads, 0, st>>>(b, ctr, ovf, nullptr, 0);
+    CK(cudaEventRecord(ctx->ev[3], st));
     k_align<true><<<ctx->grid_wide, kCtaThreads, 0, st>>>(
         b, ctr, ovf, static_cast<int32_t*>(ctx->wide_ws.p), ctx->wide_cap);
     ctx->stats.kernel_launches += 2;
+  } else {
+    CK(cudaEventRecord(ctx->ev[3], st));
   }
+  CK(cudaEventRecord(ctx->ev[4], st));
+  ctx->timed = true;
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(ctx->h_counters, ctx->counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+  return OTGPU_OK;
+}
+
+int otgpu_last_align_ms(otgpu_ctx* ctx, float ms[4]) {
+  if (!ctx || !ms) return OTGPU_ERR_ARGS;
+  if (!ctx->timed) return OTGPU_ERR_STATE;
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaEventSynchronize(ctx->ev[4]));
+  for (int i = 0; i < 4; ++i) CK(cudaEventElapsedTime(&ms[i], ctx->ev[i], ctx->ev[i + 1]));
   return OTGPU_OK;
 }
 
