@@ -21,7 +21,6 @@ using namespace otgpu;
 
 namespace {
 
-constexpr int kRingCap = 512;      // int32 slots per warp in shared memory (live width <= 509)
 constexpr int kWarpsPerCta = 8;
 constexpr int kCtaThreads = kWarpsPerCta * 32;
 constexpr uint32_t kEmptySlot = 0xffffffffu;
@@ -92,27 +91,25 @@ __global__ void __launch_bounds__(128) k_expand_regions(const uint32_t* __restri
 }
 
 __device__ __forceinline__ SeqView view2(const DevBatch& b, uint32_t r) {
-  return SeqView{b.packed + b.pk_off[r], 0};
+  return SeqView{(uint32_t)b.pk_off[r], 0};
 }
 __device__ __forceinline__ SeqView view8(const DevBatch& b, uint32_t r) {
   const uint64_t o = b.read_off[r];
-  return SeqView{reinterpret_cast<const uint32_t*>(b.bases + (o & ~3ull)), (int)(o & 3ull)};
+  return SeqView{(uint32_t)(o >> 2), (int)(o & 3ull)};
 }
 
 template <bool WIDE>
-__global__ void __launch_bounds__(kCtaThreads)
+__global__ void __launch_bounds__(kCtaThreads, 4)
 k_align(DevBatch b, Counters* __restrict__ ctr, uint32_t* __restrict__ ovf_list,
         int32_t* __restrict__ wide_ws, int wide_cap) {
   __shared__ int32_t ring_smem[WIDE ? 1 : kWarpsPerCta * kRingCap];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  int32_t* ring;
-  int mask;
-  if (WIDE) {
-    ring = wide_ws + (size_t)(blockIdx.x * kWarpsPerCta + warp) * wide_cap;
-    mask = wide_cap - 1;
+  Ring<WIDE> ring;
+  if constexpr (WIDE) {
+    ring.p = wide_ws + (size_t)(blockIdx.x * kWarpsPerCta + warp) * wide_cap;
+    ring.mask = wide_cap - 1;
   } else {
-    ring = ring_smem + warp * kRingCap;
-    mask = kRingCap - 1;
+    ring.base = (unsigned)__cvta_generic_to_shared(ring_smem + warp * kRingCap);
   }
   const unsigned long long limit = WIDE ? ctr->v[1] : b.n_pairs;
   for (;;) {
@@ -134,12 +131,14 @@ k_align(DevBatch b, Counters* __restrict__ ctr, uint32_t* __restrict__ ovf_list,
     const bool bytes = ((b.read_flag[pr.pattern] | b.read_flag[pr.text]) & 1u) != 0;
     int score;
     if (bytes) {
+      J.words = reinterpret_cast<const uint32_t*>(b.bases);
       J.P = view8(b, pr.pattern); J.T = view8(b, pr.text);
-      score = wfa_edit_pair<8, WIDE>(ring, mask, J, lane);
+      score = wfa_edit_pair<8, WIDE>(ring, J, lane);
       if (!WIDE && lane == 0) atomicAdd(&ctr->v[3], 1ull);
     } else {
+      J.words = b.packed;
       J.P = view2(b, pr.pattern); J.T = view2(b, pr.text);
-      score = wfa_edit_pair<2, WIDE>(ring, mask, J, lane);
+      score = wfa_edit_pair<2, WIDE>(ring, J, lane);
     }
     __syncwarp();
     if (lane == 0) {
@@ -230,6 +229,10 @@ int upload_reads(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const u
     CK(cudaMallocHost(&ctx->h_pk_off, want));
     ctx->h_pk_off_cap = want;
   }
+  if (n_bases >= ((uint64_t)1 << 34)) {  // kernels address reads by 32-bit word index
+    snprintf(ctx->err, sizeof(ctx->err), "batch exceeds 16 GiB of bases; split it");
+    return OTGPU_ERR_ARGS;
+  }
   uint64_t* pk = static_cast<uint64_t*>(ctx->h_pk_off);
   uint64_t words = 0;
   uint32_t max_len = 0;
@@ -270,7 +273,7 @@ int size_launch(otgpu_ctx* ctx) {
     ctx->grid_main = ctx->n_sm * per_sm;
   }
   // wide fallback: ring must hold every diagonal of the longest possible pair
-  const int need = next_pow2(2 * (int)ctx->max_len + 16);
+  const int need = next_pow2(2 * (int)ctx->max_len + 64);
   int grid_wide = ctx->n_sm * 2;
   const size_t budget = (size_t)4 << 30;
   while (grid_wide > 1 && (size_t)grid_wide * kWarpsPerCta * need * 4 > budget) grid_wide /= 2;
