@@ -1,0 +1,332 @@
+// otter_b200/host/analignments_b200.cpp — see analignments_b200.hpp.
+//
+// Every alignment below runs on the GPU (include/otter_b200.h); the host only decides WHICH
+// alignment the reference would run for a pair (src/analignments.cpp:62-101) and forms the FP64
+// result with the reference's own expressions, so dissimilarities are bit-identical.
+#include "analignments_b200.hpp"
+
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <iostream>
+
+#include "otter_b200.h"
+
+namespace {
+
+// What align_anreads (src/analignments.cpp:62-101) does for (x, y), minus the alignment itself.
+struct PairPlan {
+  enum Kind { kNone, kE2E, kEndsFree } kind;
+  bool pattern_is_y;  // which read is the pattern
+  int pb, pe;         // ends-free: pattern begin/end free
+  double denom;       // score / denom is the returned distance
+};
+
+PairPlan plan_pair(const ANREAD& x, const ANREAD& y) {
+  PairPlan p{PairPlan::kNone, false, 0, 0, 1.0};
+  if ((x.is_spanning() && y.is_spanning()) || (y.is_spanning() && x.seq.size() >= y.seq.size())) {
+    const bool x_is_smallest = x.seq.size() < y.seq.size();  // :67
+    p.kind = PairPlan::kE2E;
+    p.pattern_is_y = x_is_smallest;  // alignEnd2End(longer, shorter), tie -> x is the pattern (:70)
+    p.denom = x_is_smallest ? (double)y.seq.size() : (double)x.seq.size();
+  } else if (y.is_spanning()) {  // x shorter and not spanning (:82-98; length_diff > 0 here)
+    const int length_diff = (int)y.seq.size() - (int)x.seq.size();
+    p.kind = PairPlan::kEndsFree;
+    p.pattern_is_y = true;
+    if (x.is_spanning_l) { p.pb = 0; p.pe = length_diff; }
+    else if (x.is_spanning_r) { p.pb = length_diff; p.pe = 0; }
+    else { p.pb = length_diff / 2; p.pe = length_diff / 2; }
+    p.denom = (double)x.seq.size();
+  }
+  return p;
+}
+
+[[noreturn]] void die(const char* what, int st, otgpu_ctx* ctx) {
+  std::cerr << "ERROR: otter_b200 " << what << ": " << otgpu_strerror(st) << " ("
+            << (ctx ? otgpu_last_cuda_error(ctx) : "") << ")" << std::endl;
+  exit(1);  // the reference's convention for fatal conditions (src/analignments.cpp:146-153)
+}
+
+// Reads of a batch laid out for the C ABI (pinned when the device is there).
+struct Staging {
+  uint8_t* bases = nullptr;
+  size_t cap = 0;
+  std::vector<uint64_t> off;
+  std::vector<uint32_t> len;
+  uint64_t used = 0;
+  ~Staging() { if (bases) otgpu_host_free(bases); }
+  void reserve(size_t n) {
+    if (n <= cap) return;
+    if (bases) otgpu_host_free(bases);
+    void* p = nullptr;
+    size_t want = n + n / 4 + 4096;
+    int st = otgpu_host_alloc(want, &p);
+    if (st != OTGPU_OK) die("pinned allocation", st, nullptr);
+    bases = static_cast<uint8_t*>(p);
+    cap = want;
+  }
+  void clear() { off.clear(); len.clear(); used = 0; }
+  uint32_t add(const std::string& s) {
+    off.push_back(used);
+    len.push_back((uint32_t)s.size());
+    std::memcpy(bases + used, s.data(), s.size());
+    used += s.size();
+    return (uint32_t)(off.size() - 1);
+  }
+};
+
+Staging& staging() {
+  thread_local Staging s;
+  return s;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+double align_anreads(wfa::WFAligner& aligner, ANREAD& read_x, ANREAD& read_y) {
+  if (read_x.seq == read_y.seq) return 0.0;  // :64
+  const PairPlan p = plan_pair(read_x, read_y);
+  if (p.kind == PairPlan::kNone) return -1.0;  // :100
+  std::string& pat = p.pattern_is_y ? read_y.seq : read_x.seq;
+  std::string& txt = p.pattern_is_y ? read_x.seq : read_y.seq;
+  if (p.kind == PairPlan::kE2E) aligner.alignEnd2End(pat, txt);
+  else aligner.alignEndsFree(pat, p.pb, p.pe, txt, 0, 0);
+  return aligner.getAlignmentScore() / p.denom;
+}
+
+double get_dist_anreads(const bool& ignore_haps, wfa::WFAligner& aligner, ANREAD& read_x,
+                        ANREAD& read_y) {
+  if (ignore_haps) return align_anreads(aligner, read_x, read_y);
+  if (read_x.hpt.is_defined() && read_y.hpt.is_defined()) {  // :109-111
+    if (read_x.hpt == read_y.hpt) return 0;
+    return 1.0;
+  }
+  return 1.0;  // ambiguous, set them apart (:113)
+}
+
+void fill_dist_matrix(const bool& ignore_haps, wfa::WFAligner& aligner, std::vector<ANREAD>& reads,
+                      std::vector<int>& indeces, DistMatrix& distmatrix) {
+  std::vector<RegionDistJob> one{{&reads, &indeces, &distmatrix}};
+  fill_dist_matrices(ignore_haps, aligner, one);
+}
+
+void fill_dist_matrices(const bool& ignore_haps, wfa::WFAligner& aligner,
+                        std::vector<RegionDistJob>& jobs) {
+  if (!ignore_haps) {  // haplotag rule only, no alignment (:108-114)
+    for (auto& J : jobs) {
+      auto& idx = *J.indeces;
+      for (uint32_t i = 0; i < idx.size(); ++i)
+        for (uint32_t j = i + 1; j < idx.size(); ++j)
+          J.distmatrix->set_dist(i, j, get_dist_anreads(false, aligner, (*J.reads)[idx[i]],
+                                                         (*J.reads)[idx[j]]));
+    }
+    return;
+  }
+  otgpu_ctx* ctx = aligner.context();
+  if (!ctx) die("fill_dist_matrix", OTGPU_ERR_NO_DEVICE, nullptr);
+  Staging& S = staging();
+  size_t total = 0;
+  bool all_spanning = true;
+  for (auto& J : jobs)
+    for (int i : *J.indeces) {
+      total += (*J.reads)[i].seq.size();
+      all_spanning &= (*J.reads)[i].is_spanning();
+    }
+  S.reserve(total + 64);
+  S.clear();
+  std::vector<uint32_t> region_start(jobs.size() + 1, 0);
+  std::vector<uint64_t> score_off(jobs.size(), 0);
+  uint64_t n_scores = 0;
+  for (size_t g = 0; g < jobs.size(); ++g) {
+    for (int i : *jobs[g].indeces) S.add((*jobs[g].reads)[i].seq);
+    region_start[g + 1] = (uint32_t)S.off.size();
+    score_off[g] = n_scores;
+    const uint64_t n = jobs[g].indeces->size();
+    n_scores += n * (n ? n - 1 : 0) / 2;
+  }
+  std::vector<int32_t> scores(n_scores);
+  if (all_spanning) {
+    // every pair is alignEnd2End(longer, shorter): pairs are expanded on the device
+    int st = otgpu_region_edit_scores(ctx, S.bases, S.used, S.off.data(), S.len.data(),
+                                      (uint32_t)S.off.size(), region_start.data(),
+                                      (uint32_t)jobs.size(), score_off.data(), n_scores,
+                                      scores.data());
+    if (st != OTGPU_OK) die("fill_dist_matrix", st, ctx);
+    for (size_t g = 0; g < jobs.size(); ++g) {
+      auto& idx = *jobs[g].indeces;
+      auto& reads = *jobs[g].reads;
+      const int32_t* sc = scores.data() + score_off[g];
+      size_t q = 0;
+      for (uint32_t i = 0; i < idx.size(); ++i)
+        for (uint32_t j = i + 1; j < idx.size(); ++j, ++q) {
+          const size_t lx = reads[idx[i]].seq.size(), ly = reads[idx[j]].seq.size();
+          const double largest = lx < ly ? (double)ly : (double)lx;  // :68
+          // equal strings score 0, and 0/largest == 0.0 == the :64 shortcut
+          jobs[g].distmatrix->set_dist(i, j, sc[q] / largest);       // :71-72
+        }
+    }
+    return;
+  }
+  // general case: some valid reads are not spanning -> per-pair plan, explicit pair list
+  std::vector<otgpu_pair> pairs;
+  std::vector<PairPlan> plans;
+  pairs.reserve(n_scores);
+  plans.reserve(n_scores);
+  for (size_t g = 0; g < jobs.size(); ++g) {
+    auto& idx = *jobs[g].indeces;
+    auto& reads = *jobs[g].reads;
+    for (uint32_t i = 0; i < idx.size(); ++i)
+      for (uint32_t j = i + 1; j < idx.size(); ++j) {
+        const PairPlan p = plan_pair(reads[idx[i]], reads[idx[j]]);
+        const uint32_t rx = region_start[g] + i, ry = region_start[g] + j;
+        plans.push_back(p);
+        if (p.kind == PairPlan::kNone) continue;
+        otgpu_pair pr;
+        pr.pattern = p.pattern_is_y ? ry : rx;
+        pr.text = p.pattern_is_y ? rx : ry;
+        pr.pattern_begin_free = p.kind == PairPlan::kEndsFree ? p.pb : -1;
+        pr.pattern_end_free = p.pe;
+        pr.text_begin_free = pr.text_end_free = 0;
+        pairs.push_back(pr);
+      }
+  }
+  std::vector<int32_t> sc(pairs.size());
+  int st = otgpu_edit_scores(ctx, S.bases, S.used, S.off.data(), S.len.data(),
+                             (uint32_t)S.off.size(), pairs.data(), pairs.size(), sc.data());
+  if (st != OTGPU_OK) die("fill_dist_matrix", st, ctx);
+  size_t q = 0, a = 0;
+  for (size_t g = 0; g < jobs.size(); ++g) {
+    auto& idx = *jobs[g].indeces;
+    auto& reads = *jobs[g].reads;
+    for (uint32_t i = 0; i < idx.size(); ++i)
+      for (uint32_t j = i + 1; j < idx.size(); ++j, ++q) {
+        double d;
+        if (reads[idx[i]].seq == reads[idx[j]].seq) {
+          d = 0.0;  // :64 comes first, whatever the spanning flags say
+          if (plans[q].kind != PairPlan::kNone) ++a;
+        } else if (plans[q].kind == PairPlan::kNone) {
+          d = -1.0;
+        } else {
+          d = sc[a++] / plans[q].denom;
+        }
+        jobs[g].distmatrix->set_dist(i, j, d);
+      }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+void invalid_reassignment(const bool& ignore_haps, const double& min_sim, const double& max_error,
+                          const int& total_alleles, std::vector<ANREAD>& reads,
+                          wfa::WFAligner& aligner, std::vector<int>& labels) {
+  std::vector<RegionReassignJob> one{{&reads, &labels, total_alleles}};
+  invalid_reassignments(ignore_haps, min_sim, max_error, aligner, one);
+}
+
+void invalid_reassignments(const bool& ignore_haps, const double& min_sim,
+                           const double& max_error, wfa::WFAligner& aligner,
+                           std::vector<RegionReassignJob>& jobs) {
+  (void)ignore_haps;  // the reference always aligns here: get_dist_anreads(true, ...) (:144)
+  otgpu_ctx* ctx = aligner.context();
+  if (!ctx) die("invalid_reassignment", OTGPU_ERR_NO_DEVICE, nullptr);
+  Staging& S = staging();
+  size_t total = 0;
+  for (auto& J : jobs)
+    for (auto& r : *J.reads) total += r.seq.size();
+  S.reserve(total + 64);
+  S.clear();
+  std::vector<uint32_t> base(jobs.size());
+  for (size_t g = 0; g < jobs.size(); ++g) {
+    base[g] = (uint32_t)S.off.size();
+    for (auto& r : *jobs[g].reads) S.add(r.seq);
+  }
+  // pass 1: every alignment the reference could run: unlabeled read i against every spanning
+  // read j.  The reference walks reads in order and updates labels in place (:131-176), so a
+  // spanning read labelled earlier in the loop becomes a target for later reads (possible with
+  // --haps, where spanning reads without haplotag start unlabeled); aligning against ALL spanning
+  // reads up front covers that, and pass 2 replays the reference's loop on the live labels.
+  std::vector<otgpu_pair> pairs;
+  std::vector<PairPlan> plans;             // one per candidate (i,j)
+  std::vector<int64_t> plan_score;         // index into sc[] or -1
+  std::vector<std::vector<int64_t>> table(jobs.size());  // per region: [u * n + j] -> plan index
+  std::vector<std::vector<int>> unl(jobs.size());
+  for (size_t g = 0; g < jobs.size(); ++g) {
+    auto& reads = *jobs[g].reads;
+    auto& labels = *jobs[g].labels;
+    const int n = (int)labels.size();
+    for (int i = 0; i < n; ++i)
+      if (labels[i] < 0) unl[g].push_back(i);
+    table[g].assign(unl[g].size() * (size_t)n, -1);
+    for (size_t u = 0; u < unl[g].size(); ++u) {
+      const int i = unl[g][u];
+      for (int j = 0; j < n; ++j) {
+        if (i == j || !reads[j].is_spanning()) continue;
+        PairPlan p = plan_pair(reads[i], reads[j]);
+        if (reads[i].seq == reads[j].seq) p.kind = PairPlan::kNone, p.denom = 0.0;  // :64 -> 0.0
+        table[g][u * n + j] = (int64_t)plans.size();
+        plans.push_back(p);
+        if (p.kind == PairPlan::kNone) {
+          plan_score.push_back(-1);
+          continue;
+        }
+        plan_score.push_back((int64_t)pairs.size());
+        otgpu_pair pr;
+        pr.pattern = base[g] + (p.pattern_is_y ? j : i);
+        pr.text = base[g] + (p.pattern_is_y ? i : j);
+        pr.pattern_begin_free = p.kind == PairPlan::kEndsFree ? p.pb : -1;
+        pr.pattern_end_free = p.pe;
+        pr.text_begin_free = pr.text_end_free = 0;
+        pairs.push_back(pr);
+      }
+    }
+  }
+  std::vector<int32_t> sc(pairs.size());
+  if (!pairs.empty()) {
+    int st = otgpu_edit_scores(ctx, S.bases, S.used, S.off.data(), S.len.data(),
+                               (uint32_t)S.off.size(), pairs.data(), pairs.size(), sc.data());
+    if (st != OTGPU_OK) die("invalid_reassignment", st, ctx);
+  }
+  // pass 2: the reference's loop (:131-176) on the live labels, scores looked up from pass 1
+  for (size_t g = 0; g < jobs.size(); ++g) {
+    auto& reads = *jobs[g].reads;
+    auto& labels = *jobs[g].labels;
+    const int total_alleles = jobs[g].total_alleles;
+    const int n = (int)labels.size();
+    for (size_t u = 0; u < unl[g].size(); ++u) {
+      const int i = unl[g][u];
+      std::vector<double> max_sim(total_alleles, 0.0);
+      for (int j = 0; j < n; ++j) {
+        if (i == j || labels[j] < 0 || !reads[j].is_spanning()) continue;
+        const int64_t pi = table[g][u * n + j];
+        const PairPlan& p = plans[pi];
+        double dist;
+        if (p.kind == PairPlan::kNone) dist = (p.denom == 0.0) ? 0.0 : -1.0;
+        else dist = sc[plan_score[pi]] / p.denom;
+        if (dist < 0) {  // :145-153
+          std::cerr << "ERROR: unexpected distance for the following alignment:\n";
+          std::cerr << reads[i].name << '\t' << reads[i].is_spanning() << '\n';
+          std::cerr << reads[i].seq << '\n';
+          std::cerr << reads[j].name << '\t' << reads[j].is_spanning() << '\n';
+          std::cerr << reads[j].seq << std::endl;
+          exit(1);
+        }
+        const double sim = 1 - dist;
+        if (sim > max_sim[labels[j]]) max_sim[labels[j]] = sim;
+      }
+      int max_sim_label = 0;
+      for (int j = 1; j < total_alleles; ++j)
+        if (max_sim[j] > max_sim[max_sim_label]) max_sim_label = j;
+      int same_max_sim = 0;
+      for (const auto& s : max_sim)
+        if (s == max_sim[max_sim_label]) ++same_max_sim;
+      if (same_max_sim == 1 && max_sim[max_sim_label] >= min_sim) {
+        double min_diff = 1.0;
+        for (int j = 0; j < total_alleles; ++j)
+          if (max_sim_label != j) {
+            const double diff = max_sim[max_sim_label] - max_sim[j];
+            if (diff < min_diff) min_diff = diff;
+          }
+        if (min_diff >= max_error) labels[i] = max_sim_label;
+      }
+    }
+  }
+}

@@ -1,0 +1,83 @@
+// otter_b200/host/host_capi.cpp — flat extern "C" entry points over the C++ host layer so the
+// Python parity tests (ctypes) can drive the reference-shaped C++ functions
+// (fill_dist_matrix, invalid_reassignment, align_anreads) exactly as otter would.
+#include <cstdint>
+#include <cstring>
+#include <memory>
+
+#include "analignments_b200.hpp"
+
+namespace {
+std::vector<ANREAD> build_reads(const char* bases, const uint64_t* off, const uint32_t* len,
+                                const uint8_t* span, uint32_t first, uint32_t last) {
+  std::vector<ANREAD> reads;
+  reads.reserve(last - first);
+  for (uint32_t i = first; i < last; ++i) {
+    ANREAD r("r" + std::to_string(i), std::string(bases + off[i], len[i]));
+    r.is_spanning_l = span ? (span[i] & 1) != 0 : true;
+    r.is_spanning_r = span ? (span[i] & 2) != 0 : true;
+    reads.emplace_back(std::move(r));
+  }
+  return reads;
+}
+wfa::WFAlignerEdit& aligner() {
+  static thread_local std::unique_ptr<wfa::WFAlignerEdit> a;
+  if (!a) a.reset(new wfa::WFAlignerEdit(wfa::WFAligner::Score, wfa::WFAligner::MemoryMed));
+  return *a;
+}
+}  // namespace
+
+extern "C" {
+
+int othost_have_device() { return aligner().context() != nullptr; }
+
+double othost_align_anreads(const char* x, uint32_t xlen, int xspan, const char* y, uint32_t ylen,
+                            int yspan) {
+  ANREAD rx("x", std::string(x, xlen)), ry("y", std::string(y, ylen));
+  rx.is_spanning_l = xspan & 1; rx.is_spanning_r = xspan & 2;
+  ry.is_spanning_l = yspan & 1; ry.is_spanning_r = yspan & 2;
+  return align_anreads(aligner(), rx, ry);
+}
+
+// One region through the reference-shaped fill_dist_matrix.
+void othost_fill_dist_matrix(const char* bases, const uint64_t* off, const uint32_t* len,
+                             const uint8_t* span, uint32_t n_reads, const int* indeces,
+                             uint32_t n_idx, double* out) {
+  auto reads = build_reads(bases, off, len, span, 0, n_reads);
+  std::vector<int> idx(indeces, indeces + n_idx);
+  DistMatrix dm(n_idx);
+  fill_dist_matrix(true, aligner(), reads, idx, dm);
+  if (!dm.values.empty()) std::memcpy(out, dm.values.data(), dm.values.size() * sizeof(double));
+}
+
+// Many regions (all reads valid) through fill_dist_matrices: one launch.
+void othost_fill_dist_matrices(const char* bases, const uint64_t* off, const uint32_t* len,
+                               const uint8_t* span, const uint32_t* region_start,
+                               uint32_t n_regions, double* out, const uint64_t* out_off) {
+  std::vector<std::vector<ANREAD>> reads(n_regions);
+  std::vector<std::vector<int>> idx(n_regions);
+  std::vector<DistMatrix> dms;
+  dms.reserve(n_regions);
+  std::vector<RegionDistJob> jobs;
+  for (uint32_t g = 0; g < n_regions; ++g) {
+    reads[g] = build_reads(bases, off, len, span, region_start[g], region_start[g + 1]);
+    idx[g].resize(reads[g].size());
+    for (size_t i = 0; i < idx[g].size(); ++i) idx[g][i] = (int)i;
+    dms.emplace_back((uint32_t)reads[g].size());
+  }
+  for (uint32_t g = 0; g < n_regions; ++g) jobs.push_back({&reads[g], &idx[g], &dms[g]});
+  fill_dist_matrices(true, aligner(), jobs);
+  for (uint32_t g = 0; g < n_regions; ++g)
+    if (!dms[g].values.empty())
+      std::memcpy(out + out_off[g], dms[g].values.data(), dms[g].values.size() * sizeof(double));
+}
+
+void othost_invalid_reassignment(const char* bases, const uint64_t* off, const uint32_t* len,
+                                 const uint8_t* span, uint32_t n_reads, double min_sim,
+                                 double max_error, int total_alleles, int* labels) {
+  auto reads = build_reads(bases, off, len, span, 0, n_reads);
+  std::vector<int> lab(labels, labels + n_reads);
+  invalid_reassignment(true, min_sim, max_error, total_alleles, reads, aligner(), lab);
+  std::memcpy(labels, lab.data(), n_reads * sizeof(int));
+}
+}

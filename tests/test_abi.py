@@ -1,0 +1,98 @@
+"""CPU tests of the boundary: the C-ABI library loads, exports every symbol the header declares,
+and fails loudly (no fallback) when there is no device."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_symbols():
+    src = open(os.path.join(ROOT, "include", "otter_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(otgpu_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol(built):
+    import otter_b200
+    from otter_b200 import capi
+    l = otter_b200.lib()
+    syms = header_symbols()
+    assert len(syms) >= 18
+    for s in syms:
+        assert hasattr(l, s), f"{s} declared in include/otter_b200.h but not exported"
+    assert sorted(capi.SYMBOLS) == syms, "otter_b200/capi.py binding list out of sync with the header"
+    assert l.otgpu_abi_version() == 1
+
+
+def test_library_is_built_for_sm_100a(built):
+    import subprocess
+    import otter_b200
+    out = subprocess.run(["cuobjdump", "-lelf", otter_b200.LIB_PATH], capture_output=True, text=True)
+    if out.returncode != 0:
+        pytest.skip("cuobjdump unavailable")
+    assert "sm_100a" in out.stdout
+
+
+def test_host_layer_exports(built):
+    l = C.CDLL(os.path.join(ROOT, "otter_b200", "lib", "libotter_b200_host.so"))
+    for s in ("othost_fill_dist_matrix", "othost_fill_dist_matrices", "othost_invalid_reassignment",
+              "othost_align_anreads", "othost_have_device"):
+        assert hasattr(l, s)
+
+
+def test_no_device_means_error_not_fallback(built):
+    import otter_b200
+    l = otter_b200.lib()
+    if l.otgpu_device_count() > 0:
+        pytest.skip("a device is present")
+    h = C.c_void_p()
+    assert l.otgpu_create(0, C.byref(h)) == 2  # OTGPU_ERR_NO_DEVICE
+    assert not h.value
+    assert b"no CPU fallback" in l.otgpu_strerror(2)
+    with pytest.raises(otter_b200.OtgpuError):
+        otter_b200.Context(0)
+    p = C.c_void_p()
+    assert l.otgpu_host_alloc(64, C.byref(p)) == 2
+    # NULL context is an argument error everywhere, never a crash
+    assert l.otgpu_batch_align(None) == 1
+    assert l.otgpu_edit_scores(None, None, 0, None, None, 0, None, 0, None) == 1
+
+
+def test_missing_library_fails_loudly(monkeypatch):
+    from otter_b200 import capi
+    monkeypatch.setattr(capi, "_lib", None)
+    monkeypatch.setattr(capi, "LIB_PATH", "/nonexistent/libotter_b200.so")
+    with pytest.raises(capi.OtgpuError, match="no CPU fallback"):
+        capi.lib()
+
+
+def test_product_never_touches_the_oracle():
+    """The product path must not import, link or load anything under oracle/."""
+    bad = []
+    for dp, _, fs in os.walk(os.path.join(ROOT, "otter_b200")):
+        for f in fs:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h")):
+                txt = open(os.path.join(dp, f), errors="ignore").read()
+                if re.search(r"wfa_oracle|libotter_ref|oracle/|wfo_|ref_shim", txt):
+                    bad.append(os.path.join(dp, f))
+    assert not bad, bad
+    for lib in ("libotter_b200.so", "libotter_b200_host.so"):
+        p = os.path.join(ROOT, "otter_b200", "lib", lib)
+        if os.path.exists(p):
+            data = open(p, "rb").read()
+            assert b"wfo_edit_score" not in data and b"ref_edit_e2e" not in data
+
+
+def test_distmatrix_index_matches_reference_layout():
+    """src/andistmat.cpp:20 index == row-major condensed order used by the region ABI."""
+    for n in (2, 3, 7, 30, 200):
+        q = 0
+        for i in range(n):
+            for j in range(i + 1, n):
+                assert ((2 * n - 3 - i) * i >> 1) + j - 1 == q
+                assert i * (2 * n - i - 1) // 2 + (j - i - 1) == q  # k_expand_regions' formula
+                q += 1

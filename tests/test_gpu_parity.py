@@ -1,0 +1,272 @@
+"""GPU parity tests (run on the B200 box): the CUDA hot path, called through the C ABI
+(include/otter_b200.h) and through the C++ host layer, against the golden vectors of the
+unmodified reference and against the oracle port on fresh inputs.  Bit-exact or fail."""
+import ctypes as C
+import itertools
+import os
+
+import numpy as np
+import pytest
+
+import support as S
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def PAIRS(rows):
+    from otter_b200.capi import PAIR_DTYPE
+    return np.array(rows, dtype=PAIR_DTYPE)
+
+
+def u8(s):
+    return np.frombuffer(s.encode() if isinstance(s, str) else s, dtype=np.uint8)
+
+
+def port_scores(reads, pairs):
+    P = S.port()
+    out = []
+    for p, t, pb, pe, tb, te in pairs.tolist():
+        x, y = S.b(reads[p]), S.b(reads[t])
+        out.append(P.wfo_edit_score(x, len(x), y, len(y), int(pb >= 0), max(pb, 0), pe, tb, te, None))
+    return np.array(out, dtype=np.int32)
+
+
+def host_lib():
+    l = C.CDLL(os.path.join(ROOT, "otter_b200", "lib", "libotter_b200_host.so"))
+    vp = C.c_void_p
+    l.othost_align_anreads.restype = C.c_double
+    l.othost_align_anreads.argtypes = [C.c_char_p, C.c_uint32, C.c_int, C.c_char_p, C.c_uint32, C.c_int]
+    l.othost_fill_dist_matrix.argtypes = [vp, vp, vp, vp, C.c_uint32, vp, C.c_uint32, vp]
+    l.othost_fill_dist_matrices.argtypes = [vp, vp, vp, vp, vp, C.c_uint32, vp, vp]
+    l.othost_invalid_reassignment.argtypes = [vp, vp, vp, vp, C.c_uint32, C.c_double, C.c_double,
+                                              C.c_int, vp]
+    return l
+
+
+# ---- C ABI vs golden ---------------------------------------------------------------------------
+def test_golden_pairs_through_c_abi(ctx, golden):
+    reads, rows = [], []
+    for g in golden["pairs"]:
+        reads += [u8(g["p"]), u8(g["t"])]
+        rows.append((len(reads) - 2, len(reads) - 1, g["pb"] if g["ef"] else -1, g["pe"], g["tb"], g["te"]))
+    bases, off, lens = S.pack_reads(reads)
+    got = ctx.edit_scores(bases, off, lens, PAIRS(rows))
+    exp = np.array([g["score"] for g in golden["pairs"]], dtype=np.int32)
+    assert np.array_equal(got, exp), np.nonzero(got != exp)
+    st = ctx.stats()
+    assert st["n_pairs_8bit"] > 0 and st["n_pairs_wide"] > 0  # both fallbacks were exercised
+
+
+def test_golden_regions_through_region_abi(ctx, golden):
+    regs = [g for g in golden["regions"] if all(s == 3 for s in g["span"])]
+    B = S.region_batch([[u8(r) for r in g["reads"]] for g in regs])
+    got = ctx.region_edit_scores(B["bases"], B["off"], B["lens"], B["region_start"], B["score_off"],
+                                 B["n_scores"])
+    q = 0
+    for g in regs:
+        n = len(g["reads"])
+        ls = [len(r) for r in g["reads"]]
+        for i, j in itertools.combinations(range(n), 2):
+            d = got[q] / float(max(ls[i], ls[j]))  # src/analignments.cpp:68-72
+            assert d == float.fromhex(g["dist"][q - int(B["score_off"][regs.index(g)])])
+            q += 1
+    assert q == B["n_scores"]
+
+
+# ---- C++ host layer (reference call surface) vs golden -----------------------------------------
+def test_golden_align_anreads_through_host_layer(built, golden):
+    H = host_lib()
+    for g in golden["anreads"]:
+        x, y = g["x"].encode(), g["y"].encode()
+        d = H.othost_align_anreads(x, len(x), g["xspan"], y, len(y), g["yspan"])
+        assert d == float.fromhex(g["dist"]), (g["xspan"], g["yspan"], len(x), len(y))
+
+
+def test_golden_fill_dist_matrix_through_host_layer(built, golden):
+    H = host_lib()
+    for g in golden["regions"]:
+        reads = [u8(r) for r in g["reads"]]
+        bases, off, lens = S.pack_reads(reads)
+        span = np.array(g["span"], dtype=np.uint8)
+        idx = np.array(g["indeces"], dtype=np.int32)
+        out = np.full(max(len(g["dist"]), 1), -7.0)
+        H.othost_fill_dist_matrix(S.ptr(bases), S.ptr(off), S.ptr(lens), S.ptr(span), len(reads),
+                                  S.ptr(idx), len(idx), S.ptr(out))
+        exp = np.array([float.fromhex(h) for h in g["dist"]])
+        assert np.array_equal(out[:len(exp)], exp)
+
+
+def test_golden_invalid_reassignment_through_host_layer(built, golden):
+    H = host_lib()
+    changed = 0
+    for g in golden["reassign"]:
+        reads = [u8(r) for r in g["reads"]]
+        bases, off, lens = S.pack_reads(reads)
+        span = np.array(g["span"], dtype=np.uint8)
+        lab = np.array(g["labels_in"], dtype=np.int32)
+        H.othost_invalid_reassignment(S.ptr(bases), S.ptr(off), S.ptr(lens), S.ptr(span), len(reads),
+                                      g["min_sim"], g["max_error"], g["total_alleles"], S.ptr(lab))
+        assert lab.tolist() == g["labels_out"]
+        changed += sum(a != b for a, b in zip(g["labels_in"], g["labels_out"]))
+    assert changed > 0
+
+
+# ---- C ABI vs the oracle port on fresh inputs ---------------------------------------------------
+@pytest.mark.parametrize("tl,e,xf,n", [(150, 0.01, 0.2, 10), (400, 0.08, 0.5, 10), (2000, 0.005, 0.2, 8),
+                                       (2000, 0.05, 0.2, 8), (900, 0.3, 0.3, 6), (6000, 0.05, 0.3, 5)])
+def test_regions_vs_port(ctx, tl, e, xf, n):
+    rng = np.random.default_rng(hash((tl, n)) % 2**32)
+    regions = [S.tr_region(rng, n, tl, e, extra_frac=xf, n_rate=0.1) for _ in range(3)]
+    B = S.region_batch(regions)
+    got = ctx.region_edit_scores(B["bases"], B["off"], B["lens"], B["region_start"], B["score_off"],
+                                 B["n_scores"])
+    P = S.port()
+    q = 0
+    for reg in regions:
+        for i, j in itertools.combinations(range(len(reg)), 2):
+            x, y = S.b(reg[i]), S.b(reg[j])
+            if len(x) < len(y):
+                x, y = y, x  # pattern = longer, tie -> read i
+            assert got[q] == P.wfo_edit_score(x, len(x), y, len(y), 0, 0, 0, 0, 0, None), (q, i, j)
+            q += 1
+
+
+def test_ends_free_forms_vs_port(ctx):
+    rng = np.random.default_rng(17)
+    reads = [r for tl, e in ((300, 0.02), (1200, 0.05), (2500, 0.01))
+             for r in S.tr_region(rng, 6, tl, e, extra_frac=0.5, n_rate=0.1)]
+    bases, off, lens = S.pack_reads(reads)
+    rows = []
+    for i in range(len(reads) - 1):
+        p, t = (i, i + 1) if lens[i] >= lens[i + 1] else (i + 1, i)
+        d = int(lens[p]) - int(lens[t])
+        rows += [(p, t, 0, d, 0, 0), (p, t, d, 0, 0, 0), (p, t, d // 2, d // 2, 0, 0),
+                 (t, p, 0, 0, 0, d), (t, p, 0, 0, d, 0), (t, p, 0, 0, d // 2, d // 2),
+                 (p, t, 0, 0, 0, 0), (p, t, -1, 0, 0, 0)]
+    pairs = PAIRS(rows)
+    got = ctx.edit_scores(bases, off, lens, pairs)
+    assert np.array_equal(got, port_scores(reads, pairs))
+
+
+def test_edge_cases_vs_port(ctx):
+    seqs = [b"", b"A", b"N", b"ACGT", b"ACGTN", b"A" * 15, b"A" * 16, b"A" * 17, b"A" * 31,
+            b"A" * 32, b"A" * 33, b"A" * 64, b"A" * 65, b"ACGT" * 300, b"ACGT" * 300 + b"A",
+            b"acgt" * 20, b"ACGT" * 20, b"\x00\xff" * 10, b"T" + b"ACGT" * 300]
+    reads = [np.frombuffer(s, dtype=np.uint8) for s in seqs]
+    bases, off, lens = S.pack_reads(reads)
+    rows = []
+    for i, j in itertools.product(range(len(reads)), repeat=2):
+        p, t = (i, j) if lens[i] >= lens[j] else (j, i)
+        rows.append((p, t, -1, 0, 0, 0))
+    pairs = PAIRS(rows)
+    got = ctx.edit_scores(bases, off, lens, pairs)
+    assert np.array_equal(got, port_scores(reads, pairs))
+    assert all(got[i * len(reads) + i] == 0 for i in range(len(reads)))  # identical -> 0 (:64)
+
+
+def test_unaligned_offsets_and_shared_reads(ctx):
+    """Reads may sit at any byte offset of the caller's buffer and be used by many pairs."""
+    rng = np.random.default_rng(23)
+    reads = S.tr_region(rng, 6, 700, 0.05, extra_frac=0.3, n_rate=0.5)
+    pad = [rng.integers(0, 7) for _ in reads]
+    chunks, off, pos = [], [], 0
+    for r, p in zip(reads, pad):
+        chunks.append(np.full(p, ord("#"), dtype=np.uint8))
+        pos += p
+        off.append(pos)
+        chunks.append(r)
+        pos += len(r)
+    bases = np.concatenate(chunks)
+    off = np.array(off, dtype=np.uint64)
+    lens = np.array([len(r) for r in reads], dtype=np.uint32)
+    rows = [((i, j) if lens[i] >= lens[j] else (j, i)) + (-1, 0, 0, 0)
+            for i, j in itertools.combinations(range(len(reads)), 2)]
+    pairs = PAIRS(rows)
+    got = ctx.edit_scores(bases, off, lens, pairs)
+    assert np.array_equal(got, port_scores(reads, pairs))
+
+
+def test_empty_and_degenerate_batches(ctx):
+    z8, z64, z32 = np.zeros(0, np.uint8), np.zeros(0, np.uint64), np.zeros(0, np.uint32)
+    assert len(ctx.edit_scores(z8, z64, z32, PAIRS([]))) == 0
+    # regions with 0, 1 and 2 reads (src/otterclust.cpp:123-148 handles n=1,2 downstream)
+    rng = np.random.default_rng(1)
+    regs = [[], S.tr_region(rng, 1, 200, 0.01), S.tr_region(rng, 2, 200, 0.01), []]
+    B = S.region_batch(regs)
+    got = ctx.region_edit_scores(B["bases"], B["off"], B["lens"], B["region_start"], B["score_off"],
+                                 B["n_scores"])
+    assert len(got) == 1
+
+
+def test_bad_arguments_are_errors(ctx):
+    import otter_b200
+    reads = [u8("ACGT"), u8("ACGA")]
+    bases, off, lens = S.pack_reads(reads)
+    with pytest.raises(otter_b200.OtgpuError):
+        ctx.edit_scores(bases, off, lens, PAIRS([(0, 2, -1, 0, 0, 0)]))  # read index out of range
+    with pytest.raises(otter_b200.OtgpuError):
+        ctx.edit_scores(bases, off, lens, PAIRS([(0, 1, 5, 0, 0, 0)]))  # free end > length
+    bad_off = off.copy()
+    bad_off[1] = 100
+    with pytest.raises(otter_b200.OtgpuError):
+        ctx.edit_scores(bases, bad_off, lens, PAIRS([(0, 1, -1, 0, 0, 0)]))
+    # the context is still usable afterwards
+    assert ctx.edit_scores(bases, off, lens, PAIRS([(0, 1, -1, 0, 0, 0)]))[0] == 1
+
+
+# ---- full-size, size-independent properties ----------------------------------------------------
+def test_full_size_properties(ctx):
+    """BASELINE config C1 at 1/10 scale plus structural properties that need no oracle:
+    determinism, region ABI == explicit-pair ABI, identical reads -> 0, score bounds,
+    |len difference| <= score <= max(len)."""
+    regions = S.make_regions("C1", seed=3, n_regions=100)
+    # duplicate one read inside a region so the equal-string case is present
+    regions[0][1] = regions[0][0].copy()
+    B = S.region_batch(regions)
+    a = ctx.region_edit_scores(B["bases"], B["off"], B["lens"], B["region_start"], B["score_off"],
+                               B["n_scores"])
+    b = ctx.region_edit_scores(B["bases"], B["off"], B["lens"], B["region_start"], B["score_off"],
+                               B["n_scores"])
+    assert np.array_equal(a, b)
+    x, y = S.pair_lengths(B)
+    assert (a >= np.abs(x - y)).all() and (a <= np.maximum(x, y)).all()
+    assert a[0] == 0
+    rows = []
+    rs = B["region_start"]
+    for g in range(len(regions)):
+        for i, j in itertools.combinations(range(rs[g], rs[g + 1]), 2):
+            rows.append(((i, j) if B["lens"][i] >= B["lens"][j] else (j, i)) + (-1, 0, 0, 0))
+    c = ctx.edit_scores(B["bases"], B["off"], B["lens"], PAIRS(rows))
+    assert np.array_equal(a, c)
+    # spot-check 200 random pairs against the port
+    rng = np.random.default_rng(0)
+    pick = rng.choice(len(rows), 200, replace=False)
+    sel = PAIRS([rows[i] for i in pick])
+    assert np.array_equal(a[pick], port_scores(B["reads"], sel))
+
+
+def test_host_layer_batched_equals_per_region(built):
+    H = host_lib()
+    rng = np.random.default_rng(8)
+    regions = [S.tr_region(rng, n, 600, 0.05, extra_frac=0.3) for n in (5, 1, 8, 2, 6)]
+    B = S.region_batch(regions)
+    out = np.zeros(B["n_scores"])
+    H.othost_fill_dist_matrices(S.ptr(B["bases"]), S.ptr(B["off"]), S.ptr(B["lens"]), None,
+                                S.ptr(B["region_start"]), len(regions), S.ptr(out),
+                                S.ptr(B["score_off"]))
+    P = S.port()
+    exp = np.zeros_like(out)
+    for g, reg in enumerate(regions):
+        bases, off, lens = S.pack_reads(reg)
+        idx = np.arange(len(reg), dtype=np.int32)
+        n = len(reg) * (len(reg) - 1) // 2
+        if n:
+            P.wfo_fill_dist_matrix(S.ptr(bases), S.ptr(off), S.ptr(lens), None, S.ptr(idx), len(reg),
+                                   S.ptr(exp[int(B["score_off"][g]):]))
+    assert np.array_equal(out, exp)
+
+
+def test_smoke_entry(built):
+    import __graft_entry__ as g
+    g.smoke()
