@@ -217,7 +217,7 @@ int next_pow2(int x) {
 // Shared front half of both upload flavours: reads + packed layout.
 int upload_reads(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const uint64_t* read_off,
                  const uint32_t* read_len, uint32_t n_reads) {
-  if (!ctx || (!bases && n_bases) || !read_off || !read_len) return OTGPU_ERR_ARGS;
+  if (!ctx || (!bases && n_bases) || ((!read_off || !read_len) && n_reads)) return OTGPU_ERR_ARGS;
   CK(cudaSetDevice(ctx->device));
   // the previous batch (device buffers, pinned staging) must be finished before it is replaced
   CK(cudaStreamSynchronize(ctx->stream));
@@ -375,7 +375,7 @@ int otgpu_batch_upload_regions(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_
                                const uint64_t* read_off, const uint32_t* read_len,
                                uint32_t n_reads, const uint32_t* region_start,
                                uint32_t n_regions, const uint64_t* score_off, uint64_t n_scores) {
-  if (!ctx || !region_start || !score_off) return OTGPU_ERR_ARGS;
+  if (!ctx || !region_start || (!score_off && n_regions)) return OTGPU_ERR_ARGS;
   ctx->resident = false;
   for (uint32_t g = 0; g < n_regions; ++g) {
     if (region_start[g + 1] < region_start[g] || region_start[g + 1] > n_reads) return OTGPU_ERR_ARGS;
