@@ -120,6 +120,22 @@ int otgpu_synchronize(otgpu_ctx* ctx);
  * kernel), ms[3] k_align wide fallback.  Waits for that align to finish. */
 int otgpu_last_align_ms(otgpu_ctx* ctx, float ms[4]);
 
+/* ---- gap-affine alignment with full CIGAR ------------------------------------------------- */
+/* What otter's `aligner2` does (src/assemble.cpp:50: WFAlignerGapAffine(4,6,2, Alignment,
+ * MemoryMed)) for local_realignment (src/analignments.cpp:24,30) and rapid_consensus (:262-281):
+ * alignEnd2End / alignEndsFree + getAlignmentCigar, for a list of pairs in one launch.
+ * Pair i's CIGAR (chars M X I D, WFA2 conventions: I consumes text, D consumes pattern) is
+ * written at cigars_out + cigar_off[i], at most cigar_off[i+1]-cigar_off[i] chars (give each pair
+ * pattern_len + text_len); cigar_len_out[i] = its length, or OTGPU_SCORE_UNFEASIBLE (-1), or
+ * OTGPU_CIGAR_OOM (-3, WF_STATUS_OOM).  scores_out[i] = getAlignmentScore() (= -penalty).
+ * Penalties: match 0, mismatch > 0, gap_open >= 0, gap_ext > 0, max(open+ext, mismatch) <= 15. */
+#define OTGPU_CIGAR_OOM (-3)
+int otgpu_affine_cigars(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                        const uint64_t* read_off, const uint32_t* read_len, uint32_t n_reads,
+                        const otgpu_pair* pairs, uint64_t n_pairs, int mismatch, int gap_open,
+                        int gap_ext, int32_t* scores_out, char* cigars_out,
+                        const uint64_t* cigar_off, int32_t* cigar_len_out);
+
 #ifdef __cplusplus
 }
 #endif

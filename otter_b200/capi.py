@@ -12,7 +12,7 @@ SYMBOLS = [
     "otgpu_last_cuda_error", "otgpu_stream", "otgpu_get_stats", "otgpu_host_alloc",
     "otgpu_host_free", "otgpu_edit_scores", "otgpu_region_edit_scores",
     "otgpu_batch_upload_regions", "otgpu_batch_upload_pairs", "otgpu_batch_align",
-    "otgpu_batch_download", "otgpu_synchronize", "otgpu_last_align_ms",
+    "otgpu_batch_download", "otgpu_synchronize", "otgpu_last_align_ms", "otgpu_affine_cigars",
 ]
 
 
@@ -70,6 +70,7 @@ def lib():
         l.otgpu_batch_download.argtypes = [vp, vp, u64]
         l.otgpu_synchronize.argtypes = [vp]
         l.otgpu_last_align_ms.argtypes = [vp, C.POINTER(C.c_float * 4)]
+        l.otgpu_affine_cigars.argtypes = [vp, vp, u64, vp, vp, u32, vp, u64, i32, i32, i32, vp, vp, vp, vp]
         _lib = l
     return _lib
 
@@ -147,6 +148,26 @@ class Context:
                                                   len(lens), _p(region_start), len(region_start) - 1,
                                                   _p(score_off), n_scores, _p(out)))
         return out
+
+    def affine_cigars(self, bases, off, lens, pairs, x=4, o=6, e=2):
+        """-> (scores int32[n], list of CIGAR bytes or negative status ints)."""
+        pairs = np.ascontiguousarray(pairs, dtype=PAIR_DTYPE)
+        n = len(pairs)
+        caps = (lens[pairs["pattern"]].astype(np.uint64) + lens[pairs["text"]].astype(np.uint64)) if n \
+            else np.zeros(0, np.uint64)
+        coff = np.zeros(n + 1, dtype=np.uint64)
+        coff[1:] = np.cumsum(caps)
+        scores = np.zeros(n, dtype=np.int32)
+        clen = np.zeros(n, dtype=np.int32)
+        cig = np.zeros(int(coff[-1]) + 1, dtype=np.uint8)
+        self._ck(self._l.otgpu_affine_cigars(self._h, _p(bases), bases.size, _p(off), _p(lens),
+                                             len(lens), _p(pairs), n, x, o, e, _p(scores), _p(cig),
+                                             _p(coff), _p(clen)))
+        out = []
+        for i in range(n):
+            out.append(cig[int(coff[i]):int(coff[i]) + int(clen[i])].tobytes() if clen[i] >= 0
+                       else int(clen[i]))
+        return scores, out
 
     def upload_regions(self, bases, off, lens, region_start, score_off, n_scores):
         self._ck(self._l.otgpu_batch_upload_regions(self._h, _p(bases), bases.size, _p(off),

@@ -11,6 +11,7 @@
 // There is no CPU path: every entry point needs a CUDA device.
 #include "../../include/otter_b200.h"
 #include "wfa_edit.cuh"
+#include "wfa_affine.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -167,6 +168,7 @@ struct otgpu_ctx {
   char err[256] = {0};
   DevBuf bases, read_off, read_len, pk_off, read_flag, packed, region_start, score_off, pairs,
       scores, ovf_list, counters, wide_ws;
+  DevBuf aff_rings, aff_slab, aff_slab2, aff_ops, cigar_off, cigars, cigar_len;  // gap-affine path
   void* h_pk_off = nullptr;  // pinned
   size_t h_pk_off_cap = 0;
   void* h_counters = nullptr;  // pinned, 4 x u64
@@ -336,7 +338,9 @@ void otgpu_destroy(otgpu_ctx* ctx) {
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   DevBuf* bufs[] = {&ctx->bases, &ctx->read_off, &ctx->read_len, &ctx->pk_off, &ctx->read_flag,
                     &ctx->packed, &ctx->region_start, &ctx->score_off, &ctx->pairs, &ctx->scores,
-                    &ctx->ovf_list, &ctx->counters, &ctx->wide_ws};
+                    &ctx->ovf_list, &ctx->counters, &ctx->wide_ws, &ctx->aff_rings,
+                    &ctx->aff_slab, &ctx->aff_slab2, &ctx->aff_ops, &ctx->cigar_off, &ctx->cigars,
+                    &ctx->cigar_len};
   for (DevBuf* b : bufs)
     if (b->p) cudaFree(b->p);
   if (ctx->h_pk_off) cudaFreeHost(ctx->h_pk_off);
@@ -541,3 +545,149 @@ int otgpu_region_edit_scores(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_ba
 }
 
 }  // extern "C"
+
+namespace {
+
+// Gap-affine + CIGAR: persistent warps, one pair per warp, per-warp HBM workspace.
+// RETRY = second pass over the pairs whose trace outgrew the first-tier slab.
+template <bool RETRY>
+__global__ void __launch_bounds__(kCtaThreads)
+k_affine(DevBatch b, Counters* __restrict__ ctr, uint32_t* __restrict__ ovf_list, AffPen pen,
+         int32_t* __restrict__ rings, int wcap, uint8_t* __restrict__ slab, uint32_t slab_bytes,
+         uint8_t* __restrict__ ops, uint32_t ops_cap, const uint64_t* __restrict__ cigar_off,
+         char* __restrict__ cigars, int32_t* __restrict__ cigar_len) {
+  __shared__ AffSlot meta_smem[kWarpsPerCta][kAffMaxScope];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const size_t gw = (size_t)blockIdx.x * kWarpsPerCta + warp;
+  AffWork W;
+  W.rings = rings + gw * 3 * (size_t)pen.scope * wcap;
+  W.wmask = wcap - 1;
+  W.slab = slab + gw * (size_t)slab_bytes;
+  W.slab_bytes = slab_bytes;
+  W.ops = ops + gw * (size_t)ops_cap;
+  W.ops_cap = ops_cap;
+  const unsigned long long limit = RETRY ? ctr->v[1] : b.n_pairs;
+  for (;;) {
+    unsigned long long q = 0;
+    if (lane == 0) q = atomicAdd(&ctr->v[RETRY ? 2 : 0], 1ull);
+    q = __shfl_sync(kFull, q, 0);
+    if (q >= limit) break;
+    const uint64_t idx = RETRY ? ovf_list[q] : q;
+    const otgpu_pair pr = b.pairs[idx];
+    EditJob J;
+    J.plen = (int)b.read_len[pr.pattern];
+    J.tlen = (int)b.read_len[pr.text];
+    J.pb = pr.pattern_begin_free; J.pe = pr.pattern_end_free;
+    J.tb = pr.text_begin_free;    J.te = pr.text_end_free;
+    const bool bytes = ((b.read_flag[pr.pattern] | b.read_flag[pr.text]) & 1u) != 0;
+    const uint64_t c0 = cigar_off[idx];
+    const int cap = (int)(cigar_off[idx + 1] - c0);
+    int score = 0, len;
+    if (bytes) {
+      J.words = reinterpret_cast<const uint32_t*>(b.bases);
+      J.P = view8(b, pr.pattern); J.T = view8(b, pr.text);
+      len = wfa_affine_pair<8>(W, meta_smem[warp], J, pen, lane, cigars + c0, cap, &score);
+    } else {
+      J.words = b.packed;
+      J.P = view2(b, pr.pattern); J.T = view2(b, pr.text);
+      len = wfa_affine_pair<2>(W, meta_smem[warp], J, pen, lane, cigars + c0, cap, &score);
+    }
+    __syncwarp();
+    if (lane == 0) {
+      if (len == kAffOverflow && !RETRY) {
+        const unsigned long long pos = atomicAdd(&ctr->v[1], 1ull);
+        ovf_list[pos] = (uint32_t)idx;
+      } else {
+        if (len == kAffOverflow) len = kAffOom;
+        cigar_len[idx] = len;
+        b.scores[idx] = len >= 0 ? score : 0;
+      }
+    }
+  }
+}
+
+}  // namespace
+
+extern "C" int otgpu_affine_cigars(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                                   const uint64_t* read_off, const uint32_t* read_len,
+                                   uint32_t n_reads, const otgpu_pair* pairs, uint64_t n_pairs,
+                                   int mismatch, int gap_open, int gap_ext, int32_t* scores_out,
+                                   char* cigars_out, const uint64_t* cigar_off,
+                                   int32_t* cigar_len_out) {
+  if (!ctx || ((!scores_out || !cigar_off || !cigar_len_out) && n_pairs)) return OTGPU_ERR_ARGS;
+  // wavefronts_penalties_set_affine (wavefront_penalties.c:86-119): X>0, O>=0, E>0
+  if (mismatch <= 0 || gap_open < 0 || gap_ext <= 0) return OTGPU_ERR_ARGS;
+  AffPen pen{mismatch, gap_open, gap_ext, 0};
+  pen.scope = (gap_open + gap_ext > mismatch ? gap_open + gap_ext : mismatch) + 1;
+  if (pen.scope > kAffMaxScope) return OTGPU_ERR_ARGS;
+  int s = otgpu_batch_upload_pairs(ctx, bases, n_bases, read_off, read_len, n_reads, pairs, n_pairs);
+  if (s != OTGPU_OK) return s;
+  if (n_pairs == 0) return OTGPU_OK;
+  const uint64_t cig_bytes = cigar_off[n_pairs];
+  for (uint64_t i = 0; i < n_pairs; ++i)
+    if (cigar_off[i + 1] < cigar_off[i]) return OTGPU_ERR_ARGS;
+  if (cig_bytes && !cigars_out) return OTGPU_ERR_ARGS;
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  // per-warp workspace: rings cover every diagonal of the longest pair, so they never alias
+  const int wcap = next_pow2(2 * (int)ctx->max_len + 64);
+  const uint32_t ops_cap = 4u * ctx->max_len + 64u;
+  const size_t ring_bytes = (size_t)3 * pen.scope * wcap * 4;
+  const uint32_t slab1 = 2u << 20;
+  int grid = ctx->n_sm * 1;
+  while (grid > 8 && (size_t)grid * kWarpsPerCta * (ring_bytes + slab1 + ops_cap) > ((size_t)24 << 30)) grid /= 2;
+  const size_t nw = (size_t)grid * kWarpsPerCta;
+  RS(aff_rings, nw * ring_bytes);
+  RS(aff_slab, nw * slab1);
+  RS(aff_ops, nw * ops_cap);
+  RS(cigar_off, (n_pairs + 1) * 8);
+  RS(cigars, cig_bytes + 16);
+  RS(cigar_len, n_pairs * 4);
+  CK(cudaMemcpyAsync(ctx->cigar_off.p, cigar_off, (n_pairs + 1) * 8, cudaMemcpyHostToDevice, st));
+  DevBatch b;
+  b.bases = static_cast<const uint8_t*>(ctx->bases.p);
+  b.read_off = static_cast<const uint64_t*>(ctx->read_off.p);
+  b.read_len = static_cast<const uint32_t*>(ctx->read_len.p);
+  b.pk_off = static_cast<const uint64_t*>(ctx->pk_off.p);
+  b.packed = static_cast<const uint32_t*>(ctx->packed.p);
+  b.read_flag = static_cast<uint32_t*>(ctx->read_flag.p);
+  b.pairs = static_cast<const otgpu_pair*>(ctx->pairs.p);
+  b.scores = static_cast<int32_t*>(ctx->scores.p);
+  b.n_pairs = n_pairs;
+  b.n_reads = n_reads;
+  CK(cudaMemsetAsync(ctx->counters.p, 0, sizeof(Counters), st));
+  CK(cudaMemsetAsync(ctx->read_flag.p, 0, (size_t)n_reads * 4, st));
+  k_pack_reads<<<n_reads, 128, 0, st>>>(b, static_cast<uint32_t*>(ctx->packed.p));
+  Counters* ctr = static_cast<Counters*>(ctx->counters.p);
+  uint32_t* ovf = static_cast<uint32_t*>(ctx->ovf_list.p);
+  k_affine<false><<<grid, kCtaThreads, 0, st>>>(
+      b, ctr, ovf, pen, static_cast<int32_t*>(ctx->aff_rings.p), wcap,
+      static_cast<uint8_t*>(ctx->aff_slab.p), slab1, static_cast<uint8_t*>(ctx->aff_ops.p), ops_cap,
+      static_cast<const uint64_t*>(ctx->cigar_off.p), static_cast<char*>(ctx->cigars.p),
+      static_cast<int32_t*>(ctx->cigar_len.p));
+  ctx->stats.kernel_launches += 2;
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(ctx->h_counters, ctx->counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  const unsigned long long n_retry = static_cast<const Counters*>(ctx->h_counters)->v[1];
+  if (n_retry) {  // traces that outgrew 2 MiB: few warps, big slabs
+    const uint32_t slab2 = 256u << 20;
+    int grid2 = (int)((n_retry + kWarpsPerCta - 1) / kWarpsPerCta);
+    if (grid2 > 8) grid2 = 8;
+    RS(aff_slab2, (size_t)grid2 * kWarpsPerCta * slab2);
+    k_affine<true><<<grid2, kCtaThreads, 0, st>>>(
+        b, ctr, ovf, pen, static_cast<int32_t*>(ctx->aff_rings.p), wcap,
+        static_cast<uint8_t*>(ctx->aff_slab2.p), slab2, static_cast<uint8_t*>(ctx->aff_ops.p),
+        ops_cap, static_cast<const uint64_t*>(ctx->cigar_off.p), static_cast<char*>(ctx->cigars.p),
+        static_cast<int32_t*>(ctx->cigar_len.p));
+    ctx->stats.kernel_launches++;
+    CK(cudaGetLastError());
+  }
+  CK(cudaMemcpyAsync(scores_out, ctx->scores.p, n_pairs * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(cigar_len_out, ctx->cigar_len.p, n_pairs * 4, cudaMemcpyDeviceToHost, st));
+  if (cig_bytes) CK(cudaMemcpyAsync(cigars_out, ctx->cigars.p, cig_bytes, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  ctx->stats.n_pairs = n_pairs;
+  ctx->stats.n_pairs_wide = n_retry;
+  return OTGPU_OK;
+}

@@ -1,0 +1,344 @@
+// otter_b200/csrc/wfa_affine.cuh — warp-per-pair gap-affine WFA with full CIGAR for sm_100a.
+//
+// What otter's `aligner2` computes (reference src/assemble.cpp:50:
+// WFAlignerGapAffine(4,6,2, Alignment, MemoryMed), default WF-adaptive(10,50,1) cut-off):
+//   compute      wavefront/wavefront_compute_affine.c:88-248 (+ limits/null inputs/init-ends of
+//                wavefront/wavefront_compute.c:39-174,325-372; per-component trim :376-423)
+//   extend/term  wavefront/wavefront_extend.c:45-68,122-168,203-260,355-452
+//   cut-off      wavefront/wavefront_heuristic.c:285-328,470-509 (on M; I1/D1 clamped to M)
+//   CIGAR        wavefront/wavefront_backtrace_buffer.c:314-362 + wavefront_pcigar.c:203-266
+// The reference drags a packed CIGAR along with every cell and spills it into a linked block
+// list; what it finally emits depends only on each cell's choice of predecessor.  Here each
+// (score, diagonal) keeps one byte of choices in an HBM slab (M source, I ext/open, D ext/open),
+// the warp walks them back from the end cell and replays the ops forward with the same
+// "re-extend matches only in M state / drop the gap-closing X" rules.  Tie-breaks are the
+// reference's: gaps prefer extension on ties (:133,151), M prefers mismatch > deletion > insertion
+// (:166-177).  This path is O(reads) per region, so it is written for clarity over issue count:
+// wavefronts live in per-warp HBM rings (L1/L2 resident), lanes own consecutive diagonals.
+#pragma once
+#include "wfa_edit.cuh"
+
+namespace otgpu {
+
+constexpr int kAffMaxScope = 16;     // max(o+e, x) + 1 must fit
+constexpr int kAffOverflow = -2;     // trace slab too small (retry with a bigger one)
+constexpr int kAffOom = -3;          // even the big slab was too small (WF_STATUS_OOM)
+
+struct AffSlot {  // one score slot (score % scope): ranges + flags of M, I1, D1
+  int lo[3], hi[3];
+  int flags;  // bit c: component c exists (pointer != NULL); bit 3+c: component c is ->null
+  int pad;
+};
+
+struct AffWork {        // per-warp workspace in HBM
+  int32_t* rings;       // [3 * scope] rings of (wmask+1) int32: component-major
+  int wmask;
+  uint8_t* slab;        // step table grows from the front (8 B / score), cells from the back
+  uint32_t slab_bytes;
+  uint8_t* ops;         // reversed op list for the CIGAR replay
+  uint32_t ops_cap;
+};
+
+struct AffPen { int x, o, e, scope; };
+
+// LCP of P[v..) and T[h..) for ONE warp-uniform position, all lanes cooperating (32 windows per
+// round).  rem = min(plen - v, tlen - h).
+template <int BITS>
+__device__ __forceinline__ int lcp_uniform(const EditJob& J, int v, int h, int rem, const int lane) {
+  constexpr int WIN = Pack<BITS>::kWin;
+  int got = 0;
+  while (rem > 0) {
+    const int o = lane * WIN;
+    int mm = 0;
+    bool stop = true;
+    if (o < rem) {
+      mm = match_window<BITS>(J.words, J.P, J.T, v + o, h + o);
+      const int lim = rem - o;
+      if (mm >= lim) mm = lim;
+      else stop = mm < WIN;
+    }
+    const unsigned b = __ballot_sync(kFull, stop);
+    if (b) {
+      const int f = __ffs(b) - 1;
+      return got + f * WIN + __shfl_sync(kFull, mm, f);
+    }
+    got += 32 * WIN; v += 32 * WIN; h += 32 * WIN; rem -= 32 * WIN;
+  }
+  return got;
+}
+
+__device__ __forceinline__ bool in_bounds(int off, int k, int plen, int tlen) {
+  return (unsigned)off <= (unsigned)tlen && (unsigned)(off - k) <= (unsigned)plen;
+}
+
+__device__ __forceinline__ int aff_rd(const int32_t* ring, int mask, int lo, int hi, int k) {
+  // init-ends rule (wavefront_compute.c:325-372): outside a wavefront's own [lo,hi] reads NULL;
+  // a null input has lo=1, hi=-1 (wavefront.c:108-138) and so always reads NULL
+  return (k >= lo && k <= hi) ? ring[k & mask] : kNull;
+}
+
+// One pair on one warp.  Returns the CIGAR length (>= 0; chars written to cig[0..min(len,cap)))
+// or OTGPU_SCORE_UNFEASIBLE (-1) / kAffOverflow (-2).  *score_out = -(penalty), as
+// getAlignmentScore() reports for match = 0 (wavefront_penalties.h:66-67).
+template <int BITS>
+__device__ int wfa_affine_pair(const AffWork& W, AffSlot* __restrict__ meta, const EditJob& J,
+                               const AffPen pen, const int lane, char* __restrict__ cig,
+                               const int cig_cap, int* score_out) {
+  const int plen = J.plen, tlen = J.tlen, ak = tlen - plen;
+  const bool ef = J.pb >= 0;
+  const int scope = pen.scope, mask = W.wmask;
+  const size_t rstride = (size_t)mask + 1;
+  int2* const steps = reinterpret_cast<int2*>(W.slab);  // {lo, cell base} per score
+  uint32_t cells_top = W.slab_bytes;                    // cells grow downward from here
+  int score = 0, null_steps = 0, end_k = 0, end_off = 0;
+
+#define RING(c, slot) (W.rings + ((size_t)(c)*scope + (slot)) * rstride)
+  // ---- wavefront 0 (wavefront_align.c:113-135 / :190-245) ----
+  {
+    const int lo0 = ef ? -J.pb : 0, hi0 = ef ? J.tb : 0;
+    const int w0 = hi0 - lo0 + 1;
+    if ((uint32_t)w0 + 64 > W.slab_bytes || w0 + 8 > mask) return kAffOverflow;
+    cells_top -= (uint32_t)w0;
+    int32_t* m0 = RING(0, 0);
+    for (int k = lo0 + lane; k <= hi0; k += 32) {
+      m0[k & mask] = k > 0 ? k : 0;
+      W.slab[cells_top + (k - lo0)] = 3;  // start cell
+    }
+    if (lane == 0) {
+      for (int s = 0; s < scope; ++s) meta[s].flags = 0;
+      meta[0].lo[0] = lo0; meta[0].hi[0] = hi0; meta[0].flags = 1;
+      steps[0] = make_int2(lo0, (int)cells_top);
+    }
+    __syncwarp();
+  }
+
+  for (;;) {
+    const int sm = score % scope;
+    const int fl = meta[sm].flags;
+    // ---- extend + termination + cut-off (wavefront_extend.c:355-452) ----
+    if (!(fl & 1)) {
+      if (null_steps > scope) return -1;  // WF_STATUS_UNFEASIBLE (:369-372)
+    } else {
+      int32_t* m = RING(0, sm);
+      WfState S;
+      S.lo = meta[sm].lo[0];
+      S.hi = meta[sm].hi[0];
+      int dmin = kBigDist;
+      for (int kc = S.lo; kc <= S.hi; kc += 32) {
+        const int k = kc + lane;
+        int off = (k <= S.hi) ? m[k & mask] : kNull;
+        const bool live = off >= 0;  // M offsets are in-bounds or exactly NULL
+        const int v = off - k;
+        const int rem = live ? min(plen - v, tlen - off) : 0;
+        off += lcp_warp<BITS>(J, live ? v : 0, live ? off : 0, rem, lane);
+        bool term = false;
+        if (live) {
+          m[k & mask] = off;
+          dmin = min(dmin, plen + max(k, ak) - off);
+          if (ef) {
+            const int left_v = plen - (off - k), left_h = tlen - off;
+            term = (left_h <= 0 && left_v <= J.pe) || (left_v <= 0 && left_h <= J.te);
+          }
+        }
+        if (ef) {  // first k in ascending order wins (wavefront_extend.c:238-260)
+          const unsigned b = __ballot_sync(kFull, term);
+          if (b) {
+            const int f = __ffs(b) - 1;
+            end_k = kc + f;
+            end_off = __shfl_sync(kFull, off, f);
+            goto backtrace;
+          }
+        }
+      }
+      __syncwarp();
+      if (!ef && __any_sync(kFull, dmin == 0)) {  // offset tlen on diagonal tlen-plen (:45-68)
+        end_k = ak;
+        end_off = tlen;
+        goto backtrace;
+      }
+      if (S.lo <= S.hi) {  // wavefront_heuristic.c:470-509
+        if (S.hi - S.lo + 1 >= kMinWfLen) {
+          Ring<true> R;
+          R.p = m;
+          R.mask = mask;
+          wf_cutoff<true>(R, plen, tlen, lane, __reduce_min_sync(kFull, dmin), S);
+        }
+        if (lane == 0) {
+          AffSlot& a = meta[sm];
+          a.lo[0] = S.lo;
+          a.hi[0] = S.hi;
+          int f2 = a.flags;
+          for (int c = 1; c <= 2; ++c)  // equate I1/D1 to M (:154-165)
+            if (f2 & (1 << c)) {
+              if (S.lo > a.lo[c]) a.lo[c] = S.lo;
+              if (S.hi < a.hi[c]) a.hi[c] = S.hi;
+              if (a.lo[c] > a.hi[c]) f2 |= 8 << c;
+            }
+          a.flags = f2;
+        }
+        __syncwarp();
+      }
+    }
+
+    // ---- compute score+1 (wavefront_compute_affine.c:192-248) ----
+    ++score;
+    {
+      const int so = score % scope;
+      if ((uint32_t)(score + 1) * 8u + 64u > cells_top) return kAffOverflow;
+      const int s_mis = score - pen.x, s_open = score - pen.o - pen.e, s_ext = score - pen.e;
+      // usable input = exists and not ->null (wavefront_compute.c:88-95); else lo=1, hi=-1
+      int mm_lo = 1, mm_hi = -1, mo_lo = 1, mo_hi = -1, ie_lo = 1, ie_hi = -1, de_lo = 1, de_hi = -1;
+      bool has_mm = false, has_mo = false, has_ie = false, has_de = false;
+      if (s_mis >= 0) {
+        const AffSlot& a = meta[s_mis % scope];
+        if ((a.flags & 1) && !(a.flags & 8)) { has_mm = true; mm_lo = a.lo[0]; mm_hi = a.hi[0]; }
+      }
+      if (s_open >= 0) {
+        const AffSlot& a = meta[s_open % scope];
+        if ((a.flags & 1) && !(a.flags & 8)) { has_mo = true; mo_lo = a.lo[0]; mo_hi = a.hi[0]; }
+      }
+      if (s_ext >= 0) {
+        const AffSlot& a = meta[s_ext % scope];
+        if ((a.flags & 2) && !(a.flags & 16)) { has_ie = true; ie_lo = a.lo[1]; ie_hi = a.hi[1]; }
+        if ((a.flags & 4) && !(a.flags & 32)) { has_de = true; de_lo = a.lo[2]; de_hi = a.hi[2]; }
+      }
+      __syncwarp();
+      if (!has_mm && !has_mo && !has_ie && !has_de) {  // null step (:199-206)
+        ++null_steps;
+        if (lane == 0) {
+          meta[so].flags = 0;
+          steps[score] = make_int2(1, 0);
+        }
+        __syncwarp();
+        continue;
+      }
+      null_steps = 0;
+      // limits (wavefront_compute.c:39-69)
+      const int lo = min(min(mm_lo, mo_lo - 1), min(ie_lo + 1, de_lo - 1));
+      const int hi = max(max(mm_hi, mo_hi + 1), max(ie_hi + 1, de_hi - 1));
+      const int width = hi - lo + 1;
+      if (width + 8 > mask) return kAffOverflow;
+      if ((uint32_t)(score + 1) * 8u + 64u + (uint32_t)width > cells_top) return kAffOverflow;
+      cells_top -= (uint32_t)width;
+      const bool has_i = has_mo || has_ie, has_d = has_mo || has_de;  // wavefront_compute.c:262-283
+      const int32_t* r_mm = RING(0, s_mis >= 0 ? s_mis % scope : 0);
+      const int32_t* r_mo = RING(0, s_open >= 0 ? s_open % scope : 0);
+      const int32_t* r_ie = RING(1, s_ext >= 0 ? s_ext % scope : 0);
+      const int32_t* r_de = RING(2, s_ext >= 0 ? s_ext % scope : 0);
+      int32_t* o_m = RING(0, so);
+      int32_t* o_i = RING(1, so);
+      int32_t* o_d = RING(2, so);
+      int mn[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff};
+      int mx[3] = {(int)0x80000000, (int)0x80000000, (int)0x80000000};
+      for (int kc = lo; kc <= hi; kc += 32) {
+        const int k = kc + lane;
+        if (k <= hi) {
+          const int ins_o = aff_rd(r_mo, mask, mo_lo, mo_hi, k - 1);
+          const int ins_e = aff_rd(r_ie, mask, ie_lo, ie_hi, k - 1);
+          const int del_o = aff_rd(r_mo, mask, mo_lo, mo_hi, k + 1);
+          const int del_e = aff_rd(r_de, mask, de_lo, de_hi, k + 1);
+          const bool i_ext = ins_e >= ins_o, d_ext = del_e >= del_o;  // ties prefer extend
+          const int ins = (i_ext ? ins_e : ins_o) + 1;
+          const int del = d_ext ? del_e : del_o;
+          const int mis = aff_rd(r_mm, mask, mm_lo, mm_hi, k) + 1;
+          int best = max(del, max(mis, ins));
+          int src = 0;
+          if (best == ins) src = 1;
+          if (best == del) src = 2;
+          if (best == mis) src = 0;  // last assignment wins: mismatch > deletion > insertion
+          if (has_i) o_i[k & mask] = ins;
+          if (has_d) o_d[k & mask] = del;
+          if (!in_bounds(best, k, plen, tlen)) best = kNull;
+          o_m[k & mask] = best;
+          W.slab[cells_top + (k - lo)] = (uint8_t)(src | (i_ext ? 4 : 0) | (d_ext ? 8 : 0));
+          if (best >= 0) { mn[0] = min(mn[0], k); mx[0] = max(mx[0], k); }
+          if (in_bounds(ins, k, plen, tlen)) { mn[1] = min(mn[1], k); mx[1] = max(mx[1], k); }
+          if (in_bounds(del, k, plen, tlen)) { mn[2] = min(mn[2], k); mx[2] = max(mx[2], k); }
+        }
+      }
+      // trim each component to its first/last in-bounds diagonal (wavefront_compute.c:376-423)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        mn[c] = __reduce_min_sync(kFull, mn[c]);
+        mx[c] = __reduce_max_sync(kFull, mx[c]);
+      }
+      if (lane == 0) {
+        AffSlot& a = meta[so];
+        int f2 = 1 | (has_i ? 2 : 0) | (has_d ? 4 : 0);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          a.lo[c] = mn[c];
+          a.hi[c] = mx[c];
+          if (mn[c] > mx[c]) f2 |= 8 << c;
+        }
+        a.flags = f2;
+        steps[score] = make_int2(lo, (int)cells_top);
+      }
+      __syncwarp();
+    }
+  }
+
+backtrace:
+  __syncwarp();
+  {
+    // ---- walk the choices back from the end cell (all lanes in lock-step, lane 0 stores) ----
+    const int result = score;
+    int s = score, kk = end_k, st = 0, n_ops = 0;  // st: 0 M, 1 I1, 2 D1
+    for (;;) {
+      if (st == 0 && s == 0) break;
+      const int2 se = steps[s];
+      const int c = W.slab[(uint32_t)se.y + (uint32_t)(kk - se.x)];
+      if ((uint32_t)n_ops + 2 > W.ops_cap) return kAffOverflow;
+      char op;
+      if (st == 0) {
+        if ((c & 3) == 0) { op = 'X'; s -= pen.x; }
+        else { op = 'c'; st = (c & 3) == 1 ? 1 : 2; }  // gap-closing X: marker only
+      } else if (st == 1) {
+        op = 'I';
+        if (c & 4) { s -= pen.e; kk -= 1; } else { s -= pen.o + pen.e; kk -= 1; st = 0; }
+      } else {
+        op = 'D';
+        if (c & 8) { s -= pen.e; kk += 1; } else { s -= pen.o + pen.e; kk += 1; st = 0; }
+      }
+      if (lane == 0) W.ops[n_ops] = (uint8_t)op;
+      ++n_ops;
+    }
+    __syncwarp();
+    // ---- forward replay (wavefront_backtrace_buffer.c:314-362, wavefront_pcigar.c:203-266) ----
+    int h = kk > 0 ? kk : 0, v = kk > 0 ? 0 : -kk;  // start cell of wavefront 0
+    int len = 0;
+    bool mstate = true;
+    auto fill = [&](char ch, int n) {
+      for (int i = lane; i < n; i += 32)
+        if (len + i < cig_cap) cig[len + i] = ch;
+      len += n;
+    };
+    fill('I', h);  // :334-335
+    fill('D', v);
+    for (int i = n_ops - 1; i >= 0; --i) {
+      if (mstate) {  // matches are re-extended only in the M state (:225-238)
+        const int n = lcp_uniform<BITS>(J, v, h, min(plen - v, tlen - h), lane);
+        fill('M', n);
+        v += n;
+        h += n;
+      }
+      const char op = (char)W.ops[i];
+      if (op == 'c') { mstate = true; continue; }  // back to M, nothing emitted (:250-254)
+      fill(op, 1);
+      if (op == 'X') { ++v; ++h; mstate = true; }
+      else if (op == 'I') { ++h; mstate = false; }
+      else { ++v; mstate = false; }
+    }
+    {
+      const int nm = min((end_off - end_k) - v, end_off - h);  // last stroke (:352-358)
+      if (nm > 0) { fill('M', nm); v += nm; h += nm; }
+    }
+    if (h < tlen) fill('I', tlen - h);
+    if (v < plen) fill('D', plen - v);
+    if (score_out) *score_out = -result;
+    return len;
+  }
+#undef RING
+}
+
+}  // namespace otgpu

@@ -40,3 +40,59 @@ struct RegionReassignJob {
 void invalid_reassignments(const bool& ignore_haps, const double& min_sim,
                            const double& max_error, wfa::WFAligner& aligner,
                            std::vector<RegionReassignJob>& jobs);
+
+// ---- gap-affine + CIGAR callers (reference src/analignments.cpp:11-60, 192-298) -----------------
+// One alignment request of `aligner2` (src/assemble.cpp:50).  pb < 0: alignEnd2End(pattern,text);
+// else alignEndsFree(pattern, pb, pe, text, tb, te).
+struct CigarJob {
+  const std::string* pattern;
+  const std::string* text;
+  int pb, pe, tb, te;
+};
+// All jobs in ONE launch; cigars[i] is what aligner2.getAlignmentCigar() returns after job i.
+void affine_cigars(wfa::WFAligner& aligner2, const std::vector<CigarJob>& jobs,
+                   std::vector<std::string>& cigars);
+
+// local_realignment (src/analignments.cpp:11-60) with the two reference flanks already fetched
+// (ref_left = ref[start-flank,start), ref_right = ref[end,end+flank), upper-cased as
+// FaidxInstance::fetch does).  Mutates read.seq / spanning flags exactly like the reference.
+struct RealignJob {
+  int flank;
+  double min_sim;
+  const std::string* ref_left;
+  const std::string* ref_right;
+  std::vector<ANREAD>* reads;
+};
+void local_realignments(wfa::WFAligner& aligner2, std::vector<RealignJob>& jobs);
+
+// The alignment half of rapid_consensus (src/analignments.cpp:192-281): per allele label the
+// medoid representative and, for alleles with >= 3 reads, each member's CIGAR against it, in the
+// order the reference inserts them into the partial-order graph.
+struct ConsensusPlan {
+  int rep = -1;                      // index into reads of the representative (medoid)
+  std::vector<int> members;          // reads with this label, excluding rep, ascending (:228)
+  std::vector<uint32_t> valid_reads; // valid (spanning) reads with this label, indexed to reads
+  std::vector<uint32_t> valid_pos;   // the same, indexed to valid_indeces
+  std::vector<std::string> cigars;   // one per member when members.size() + 1 > 2, else empty
+};
+struct ConsensusJob {
+  std::vector<ANREAD>* reads;
+  std::vector<int>* labels;
+  std::vector<int>* valid_indeces;
+  int total_alleles;
+  DistMatrix* valid_distmatrix;
+  std::vector<ConsensusPlan> plans;  // out: one per label
+};
+void rapid_consensus_alignments(wfa::WFAligner& aligner2, std::vector<ConsensusJob>& jobs);
+
+#ifdef OTTER_B200_IN_TREE
+#include "anfahelper.hpp"
+// Reference signatures; the alignment calls inside run batched on the GPU.
+void local_realignment(const std::string& chr, const int& start, const int& end, const int& flank,
+                       const double& min_sim, const FaidxInstance& faidx_inst,
+                       std::vector<ANREAD>& reads, wfa::WFAligner& aligner);
+void rapid_consensus(const bool& ignore_haps, std::vector<ANREAD>& reads, std::vector<int>& labels,
+                     std::vector<int>& valid_indeces, int& total_alleles,
+                     DistMatrix& valid_distmatrix, wfa::WFAligner& aligner,
+                     std::vector<ANALLELE>& alleles);
+#endif

@@ -43,6 +43,9 @@ class WFAligner {
   // the batched entry points; which CUDA device new aligners bind to (default 0).
   otgpu_ctx* context() { return ctx_; }
   bool isEdit() const { return kind_ == kEdit; }
+  int mismatch() const { return x_; }
+  int gapOpening() const { return o_; }
+  int gapExtension() const { return e_; }
   static void setDefaultDevice(int device);
 
  protected:
