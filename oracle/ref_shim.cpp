@@ -8,9 +8,24 @@
 //
 // Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
 // load this library.  The product (otter_b200/) never does.
+// Built twice by oracle/Makefile:
+//   _ref/libotter_ref.so     against WFA2-lib's own WFAligner.hpp + the reference analignments.cpp
+//                            (the pure reference: oracle and CPU baseline);
+//   _ref/libotter_intree.so  -DOTTER_B200_IN_TREE: the same reference pipeline objects
+//                            (otterclust, ankde, anppoa, anseqs, hclust-cpp) but with
+//                            otter_b200/host/{analignments,realign,wfaligner}_b200.cpp in place of
+//                            analignments.cpp + WFA2, i.e. otter running on the GPU hot path.
+//                            Used by the GPU tests to compare whole-region results (labels,
+//                            alleles) with libotter_ref.so.
 #include "bindings/cpp/WFAligner.hpp"
+#ifdef OTTER_B200_IN_TREE
+#include "analignments_b200.hpp"
+#else
 #include "analignments.hpp"
+#endif
 #include "andistmat.hpp"
+#include "anfahelper.hpp"
+#include "anppoa.hpp"
 #include "anseqs.hpp"
 #include "otterclust.hpp"
 
@@ -163,4 +178,95 @@ void ref_invalid_reassignment(const char* bases, const uint64_t* off, const uint
 }
 
 int ref_hardware_threads() { return (int)std::thread::hardware_concurrency(); }
+
+// test/ppoa_test.cpp:10-37 (runtest) with the 4-argument insert_alignment the current header has:
+// every sequence aligned end-to-end to the first with aligner2, inserted into the partial-order
+// graph, consensus with weights (n*0.4, 0.3).  Returns the consensus length.
+int ref_ppoa_consensus(const char* bases, const uint64_t* off, const uint32_t* len, uint32_t n,
+                       char* out, int cap) {
+  std::vector<std::string> seqs;
+  for (uint32_t i = 0; i < n; ++i) seqs.emplace_back(bases + off[i], len[i]);
+  PPOA poa;
+  poa.init(seqs[0]);
+  auto& aligner = tls().affine;
+  bool yes = true;
+  for (auto& seq : seqs) {
+    aligner.alignEnd2End(seqs[0], seq);
+    std::string cigar = aligner.getAlignmentCigar();
+    poa.insert_alignment(seq, cigar, yes, yes);
+  }
+  poa.adjust_weights((float)seqs.size() * 0.4, 0.3);
+  std::string consensus;
+  poa.consensus(consensus);
+  std::memcpy(out, consensus.data(), (int)consensus.size() < cap ? consensus.size() : cap);
+  return (int)consensus.size();
+}
+
+// local_realignment (src/analignments.cpp:11-60) against an indexed FASTA on disk.
+// ccoords = pairs (first, second) per read.  Outputs: new sequences concatenated in out_bases
+// (lengths in out_len) and new span bits.  Returns total bytes needed.
+uint64_t ref_local_realignment(const char* fasta, const char* chr, int start, int end, int flank,
+                               double min_sim, const char* bases, const uint64_t* off,
+                               const uint32_t* len, const uint8_t* span, const int* ccoords,
+                               uint32_t n_reads, char* out_bases, uint64_t cap, uint32_t* out_len,
+                               uint8_t* out_span) {
+  std::vector<ANREAD> reads;
+  build_reads(bases, off, len, span, 0, n_reads, reads);
+  for (uint32_t i = 0; i < n_reads; ++i) reads[i].ccoords = {ccoords[2 * i], ccoords[2 * i + 1]};
+  FaidxInstance fa;
+  fa.init(fasta);
+  local_realignment(chr, start, end, flank, min_sim, fa, reads, tls().affine);
+  fa.destroy();
+  uint64_t used = 0;
+  for (uint32_t i = 0; i < n_reads; ++i) {
+    out_len[i] = (uint32_t)reads[i].seq.size();
+    out_span[i] = (reads[i].is_spanning_l ? 1 : 0) | (reads[i].is_spanning_r ? 2 : 0);
+    if (used + reads[i].seq.size() <= cap) std::memcpy(out_bases + used, reads[i].seq.data(), reads[i].seq.size());
+    used += reads[i].seq.size();
+  }
+  return used;
+}
+
+// One region through the body of assemble_process (src/assemble.cpp:103-142) with the default
+// options of command_assemble.cpp:34-45 (no --haps): partition_valid_reads -> fill_dist_matrix ->
+// otter_hclust -> invalid_reassignment -> rapid_consensus.  Outputs the per-read labels and the
+// alleles (sequence, acov, scov, tcov, se, ic).  Returns the number of alleles (0 if no spanning
+// read), allele sequences concatenated in out_seq (lengths out_seq_len).
+int ref_assemble_region(const char* bases, const uint64_t* off, const uint32_t* len,
+                        const uint8_t* span, uint32_t n_reads, int max_alleles, int* out_labels,
+                        char* out_seq, uint64_t cap, uint32_t* out_seq_len, int* out_cov /*3 per*/,
+                        float* out_se, int* out_ic) {
+  std::vector<ANREAD> reads;
+  build_reads(bases, off, len, span, 0, n_reads, reads);
+  for (uint32_t i = 0; i < n_reads; ++i) out_labels[i] = -1;
+  bool ignore_haps = true;
+  std::vector<int> valid, invalid;
+  for (int i = 0; i < (int)reads.size(); ++i)  // partition_valid_reads, src/assemble.cpp:27-37
+    (reads[i].is_spanning() ? valid : invalid).emplace_back(i);
+  if (valid.empty()) return 0;
+  auto& A = tls();
+  DistMatrix distmatrix(valid.size());
+  if (max_alleles != 1) fill_dist_matrix(ignore_haps, A.edit, reads, valid, distmatrix);
+  ClusteringStatus clust;
+  otter_hclust(ignore_haps, max_alleles, 0.01, 500, 0.015, 0.01, 0.2, 500, 0.1, valid, distmatrix,
+               A.edit, reads, clust);
+  std::vector<int> labels(reads.size(), -1);
+  for (uint32_t i = 0; i < clust.labels.size(); ++i) labels[valid[i]] = clust.labels[i];
+  if (!invalid.empty()) invalid_reassignment(ignore_haps, 0.9, 0.01, clust.fc, reads, A.edit, labels);
+  std::vector<ANALLELE> alleles(clust.fc);
+  rapid_consensus(ignore_haps, reads, labels, valid, clust.fc, distmatrix, A.affine, alleles);
+  uint64_t used = 0;
+  for (int l = 0; l < clust.fc; ++l) {
+    out_seq_len[l] = (uint32_t)alleles[l].seq.size();
+    if (used + alleles[l].seq.size() <= cap) std::memcpy(out_seq + used, alleles[l].seq.data(), alleles[l].seq.size());
+    used += alleles[l].seq.size();
+    out_cov[3 * l] = alleles[l].acov;
+    out_cov[3 * l + 1] = alleles[l].scov;
+    out_cov[3 * l + 2] = alleles[l].tcov;
+    out_se[l] = alleles[l].se;
+  }
+  *out_ic = clust.ic;
+  for (uint32_t i = 0; i < n_reads; ++i) out_labels[i] = labels[i];
+  return clust.fc;
+}
 }

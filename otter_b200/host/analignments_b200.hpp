@@ -70,6 +70,7 @@ void local_realignments(wfa::WFAligner& aligner2, std::vector<RealignJob>& jobs)
 // order the reference inserts them into the partial-order graph.
 struct ConsensusPlan {
   int rep = -1;                      // index into reads of the representative (medoid)
+  int rep_pos = -1;                  // the same read as a position in valid_indeces
   std::vector<int> members;          // reads with this label, excluding rep, ascending (:228)
   std::vector<uint32_t> valid_reads; // valid (spanning) reads with this label, indexed to reads
   std::vector<uint32_t> valid_pos;   // the same, indexed to valid_indeces

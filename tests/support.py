@@ -16,6 +16,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 PORT_SO = os.path.join(ROOT, "oracle", "libwfa_oracle.so")
 REF_SO = os.path.join(ROOT, "oracle", "_ref", "libotter_ref.so")
+INTREE_SO = os.path.join(ROOT, "oracle", "_ref", "libotter_intree.so")
 
 c_char_p, c_int, c_u32, c_u64, c_dbl = C.c_char_p, C.c_int, C.c_uint32, C.c_uint64, C.c_double
 vp = C.c_void_p
@@ -59,10 +60,8 @@ def have_ref():
     return os.path.exists(REF_SO)
 
 
-def ref():
-    global _ref
-    if _ref is None:
-        l = C.CDLL(REF_SO)
+def _bind_ref(l):
+    if True:
         l.ref_edit_e2e.restype = c_int
         l.ref_edit_e2e.argtypes = [c_char_p, c_int, c_char_p, c_int]
         l.ref_edit_endsfree.restype = c_int
@@ -78,8 +77,59 @@ def ref():
         l.ref_fill_dist_matrix_regions.argtypes = [vp, vp, vp, vp, c_u32, vp, vp, c_int]
         l.ref_invalid_reassignment.restype = None
         l.ref_invalid_reassignment.argtypes = [vp, vp, vp, vp, c_u32, c_dbl, c_dbl, c_int, vp]
-        _ref = l
+        l.ref_ppoa_consensus.restype = c_int
+        l.ref_ppoa_consensus.argtypes = [vp, vp, vp, c_u32, c_char_p, c_int]
+        l.ref_local_realignment.restype = c_u64
+        l.ref_local_realignment.argtypes = [c_char_p, c_char_p, c_int, c_int, c_int, c_dbl, vp, vp, vp,
+                                            vp, vp, c_u32, vp, c_u64, vp, vp]
+        l.ref_assemble_region.restype = c_int
+        l.ref_assemble_region.argtypes = [vp, vp, vp, vp, c_u32, c_int, vp, vp, c_u64, vp, vp, vp, vp]
+    return l
+
+
+def ref():
+    """The unmodified reference (CPU)."""
+    global _ref
+    if _ref is None:
+        _ref = _bind_ref(C.CDLL(REF_SO))
     return _ref
+
+
+_intree = None
+
+
+def have_intree():
+    return os.path.exists(INTREE_SO)
+
+
+def intree():
+    """The reference pipeline (otterclust, anppoa, ...) running on the GPU hot path."""
+    global _intree
+    if _intree is None:
+        _intree = _bind_ref(C.CDLL(INTREE_SO))
+    return _intree
+
+
+def assemble_region(lib, reads, span, max_alleles=2):
+    """Run one region through src/assemble.cpp:103-142 (via ref_shim) -> dict."""
+    bases, off, lens = pack_reads(reads)
+    n = len(reads)
+    sp = np.array(span, dtype=np.uint8)
+    labels = np.zeros(n, dtype=np.int32)
+    cap = int(lens.sum()) * 4 + 1024
+    seq = np.zeros(cap, dtype=np.uint8)
+    seq_len = np.zeros(max(n, 4), dtype=np.uint32)
+    cov = np.zeros(3 * max(n, 4), dtype=np.int32)
+    se = np.zeros(max(n, 4), dtype=np.float32)
+    ic = c_int(0)
+    k = lib.ref_assemble_region(ptr(bases), ptr(off), ptr(lens), ptr(sp), n, max_alleles, ptr(labels),
+                                ptr(seq), cap, ptr(seq_len), ptr(cov), ptr(se), C.byref(ic))
+    alleles, pos = [], 0
+    for a in range(k):
+        alleles.append(seq[pos:pos + int(seq_len[a])].tobytes().decode())
+        pos += int(seq_len[a])
+    return dict(n_alleles=k, labels=labels.tolist(), alleles=alleles, cov=cov[:3 * k].tolist(),
+                se=[float(x).hex() for x in se[:k]], ic=ic.value)
 
 
 from otter_b200.synth import (ALPHA, rand_seq, mutate, tr_region, pack_reads,  # noqa: E402,F401
