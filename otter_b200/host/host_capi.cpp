@@ -80,4 +80,42 @@ void othost_invalid_reassignment(const char* bases, const uint64_t* off, const u
   invalid_reassignment(true, min_sim, max_error, total_alleles, reads, aligner(), lab);
   std::memcpy(labels, lab.data(), n_reads * sizeof(int));
 }
+
+// aligner2 facade (WFAlignerGapAffine(4,6,2, Alignment, MemoryMed)), one pair.
+int othost_affine_cigar(const char* p, int plen, const char* t, int tlen, int endsfree, int pb,
+                        int pe, int tb, int te, int* score, int* status, char* cigar, int cap) {
+  static thread_local std::unique_ptr<wfa::WFAlignerGapAffine> a;
+  if (!a) a.reset(new wfa::WFAlignerGapAffine(4, 6, 2, wfa::WFAligner::Alignment, wfa::WFAligner::MemoryMed));
+  const int st = endsfree ? a->alignEndsFree(p, plen, pb, pe, t, tlen, tb, te)
+                          : a->alignEnd2End(p, plen, t, tlen);
+  if (status) *status = st;
+  if (score) *score = a->getAlignmentScore();
+  const std::string c = a->getAlignmentCigar();
+  if (cigar && cap > 0) std::memcpy(cigar, c.data(), (int)c.size() < cap ? c.size() : cap);
+  return (int)c.size();
+}
+
+// local_realignment with pre-fetched flanks (local_realignments, one job).  ccoords = (first,
+// second) per read.  New sequences are concatenated into out_bases; returns total bytes needed.
+uint64_t othost_local_realignment(int flank, double min_sim, const char* ref_left, uint32_t ll,
+                                  const char* ref_right, uint32_t rl, const char* bases,
+                                  const uint64_t* off, const uint32_t* len, const uint8_t* span,
+                                  const int* ccoords, uint32_t n_reads, char* out_bases,
+                                  uint64_t cap, uint32_t* out_len, uint8_t* out_span) {
+  static thread_local std::unique_ptr<wfa::WFAlignerGapAffine> a;
+  if (!a) a.reset(new wfa::WFAlignerGapAffine(4, 6, 2, wfa::WFAligner::Alignment, wfa::WFAligner::MemoryMed));
+  auto reads = build_reads(bases, off, len, span, 0, n_reads);
+  for (uint32_t i = 0; i < n_reads; ++i) reads[i].ccoords = {ccoords[2 * i], ccoords[2 * i + 1]};
+  const std::string L(ref_left, ll), R(ref_right, rl);
+  std::vector<RealignJob> one{{flank, min_sim, &L, &R, &reads}};
+  local_realignments(*a, one);
+  uint64_t used = 0;
+  for (uint32_t i = 0; i < n_reads; ++i) {
+    out_len[i] = (uint32_t)reads[i].seq.size();
+    out_span[i] = (reads[i].is_spanning_l ? 1 : 0) | (reads[i].is_spanning_r ? 2 : 0);
+    if (used + reads[i].seq.size() <= cap) std::memcpy(out_bases + used, reads[i].seq.data(), reads[i].seq.size());
+    used += reads[i].seq.size();
+  }
+  return used;
+}
 }

@@ -58,3 +58,92 @@ def gen_cigars(R, rng, out):
                   ("ACGTACGTACGT", "ACGTTTTTACGTACGT")):
         sc, cg = ref_cigar(R, a.encode(), b_.encode(), 0, 0, 0, 0, 0)
         out["cigars"].append(dict(p=a, t=b_, ef=0, pb=0, pe=0, tb=0, te=0, score=sc, cigar=cg))
+
+
+def gen_realign(R, rng, out):
+    """local_realignment against an indexed FASTA written to a temp dir."""
+    with tempfile.TemporaryDirectory() as td:
+        ref = S.rand_seq(rng, 3000)
+        motif = S.rand_seq(rng, 3)
+        start, end, flank = 1000, 1000 + 3 * 80, 100
+        ref[start:end] = np.tile(motif, 80)
+        fa = os.path.join(td, "ref.fa")
+        with open(fa, "w") as f:
+            f.write(">chr1\n")
+            s = S.b(ref).decode()
+            for i in range(0, len(s), 60):
+                f.write(s[i:i + 60] + "\n")
+        for trial in range(3):
+            reads, span, cc = [], [], []
+            for r in range(8):
+                kind = r % 4  # 0 spanning, 1 left side open, 2 right side open, 3 short clip
+                body = S.mutate(rng, ref[start - 150:end + 150].copy(), 0.02)
+                if kind == 0:
+                    reads.append(body); span.append(3); cc.append((150, len(body) - 150))
+                elif kind == 1:
+                    reads.append(body); span.append(2)
+                    cc.append((140 + int(rng.integers(0, 20)), len(body)))
+                elif kind == 2:
+                    reads.append(body); span.append(1)
+                    cc.append((0, len(body) - 140 - int(rng.integers(0, 20))))
+                else:
+                    reads.append(body[100:]); span.append(2); cc.append((50, len(body) - 100))
+            bases, off, lens = S.pack_reads(reads)
+            sp = np.array(span, dtype=np.uint8)
+            ccv = np.array(cc, dtype=np.int32).reshape(-1)
+            cap = int(lens.sum()) + 64
+            ob_ = np.zeros(cap, dtype=np.uint8)
+            ol = np.zeros(len(reads), dtype=np.uint32)
+            os_ = np.zeros(len(reads), dtype=np.uint8)
+            R.ref_local_realignment(fa.encode(), b"chr1", start, end, flank, C.c_double(0.9),
+                                    S.ptr(bases), S.ptr(off), S.ptr(lens), S.ptr(sp), S.ptr(ccv),
+                                    len(reads), S.ptr(ob_), cap, S.ptr(ol), S.ptr(os_))
+            new, pos = [], 0
+            for n in ol:
+                new.append(ob_[pos:pos + int(n)].tobytes().decode())
+                pos += int(n)
+            out["realign"].append(dict(flank=flank, min_sim=0.9,
+                                       ref_left=S.b(ref[start - flank:start]).decode(),
+                                       ref_right=S.b(ref[end:end + flank]).decode(),
+                                       reads=[S.b(r).decode() for r in reads], span=span,
+                                       ccoords=[list(c) for c in cc], out_reads=new,
+                                       out_span=os_.tolist()))
+
+
+def gen_assemble(R, rng, out):
+    """Whole regions through assemble_process' body (src/assemble.cpp:103-142)."""
+    for n_reads, e, copies in [(12, 0.01, (60, 90)), (20, 0.03, (40, 48)), (9, 0.005, (50, 50)),
+                               (30, 0.05, (100, 130)), (3, 0.01, (30, 40))]:
+        motif = S.rand_seq(rng, int(rng.integers(2, 6)))
+        fl, fr = S.rand_seq(rng, 80), S.rand_seq(rng, 80)
+        al = [np.concatenate([fl, np.tile(motif, c), fr]) for c in copies]
+        reads = [S.mutate(rng, al[int(rng.integers(0, 2))], e) for _ in range(n_reads)]
+        span = [3] * n_reads
+        for a in (0, 1):
+            r = S.mutate(rng, al[a], e)
+            cut = int(rng.integers(20, 60))
+            reads.append(r[:-cut]); span.append(1)
+            reads.append(r[cut:]); span.append(2)
+        res = S.assemble_region(R, reads, span)
+        out["assemble"].append(dict(reads=[S.b(r).decode() for r in reads], span=span, result=res))
+
+
+def main():
+    R = S.ref()
+    rng = np.random.default_rng(20261105)
+    out = {"source": "holstegelab/otter @ 2573c48e + WFA2-lib v2.2: WFAlignerGapAffine(4,6,2,"
+                     "Alignment,MemoryMed); PPOA src/anppoa.hpp; pipeline src/assemble.cpp:103-142",
+           "cigars": [], "ppoa_kat": [], "realign": [], "assemble": []}
+    gen_cigars(R, rng, out)
+    gen_realign(R, rng, out)
+    gen_assemble(R, rng, out)
+    path = os.path.join(HERE, "affine_golden.json")
+    json.dump(out, open(path, "w"))
+    chg = sum(a != b for g in out["realign"] for a, b in zip(g["reads"], g["out_reads"]))
+    print(path, os.path.getsize(path), "bytes;", len(out["cigars"]), "cigars,", len(out["ppoa_kat"]),
+          "ppoa KATs,", len(out["realign"]), "realign cases (", chg, "reads trimmed ),",
+          len(out["assemble"]), "regions:", [g["result"]["n_alleles"] for g in out["assemble"]])
+
+
+if __name__ == "__main__":
+    main()
