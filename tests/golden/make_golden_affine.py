@@ -103,8 +103,10 @@ def gen_realign(R, rng, out):
                 new.append(ob_[pos:pos + int(n)].tobytes().decode())
                 pos += int(n)
             out["realign"].append(dict(flank=flank, min_sim=0.9,
-                                       ref_left=S.b(ref[start - flank:start]).decode(),
-                                       ref_right=S.b(ref[end:end + flank]).decode(),
+                                       # faidx_fetch_seq takes an INCLUSIVE end (src/faidx.c), so
+                                       # FaidxInstance::fetch(chr, a, b) returns b - a + 1 bases
+                                       ref_left=S.b(ref[start - flank:start + 1]).decode(),
+                                       ref_right=S.b(ref[end:end + flank + 1]).decode(),
                                        reads=[S.b(r).decode() for r in reads], span=span,
                                        ccoords=[list(c) for c in cc], out_reads=new,
                                        out_span=os_.tolist()))

@@ -87,3 +87,38 @@ def test_reference_reproduces_its_ppoa_known_answers(agold):
         buf = C.create_string_buffer(1000)
         n = R.ref_ppoa_consensus(S.ptr(bases), S.ptr(off), S.ptr(lens), len(reads), buf, 1000)
         assert buf.raw[:n].decode() == kat["expected"]
+
+
+def test_golden_local_realignment_replayed_with_port(agold):
+    """local_realignment (src/analignments.cpp:11-60) replayed in Python on the port's CIGARs
+    reproduces what the reference did to the reads — pins the flank strings of the fixture
+    (faidx fetch is end-inclusive: flank + 1 bases)."""
+    for g in agold["realign"]:
+        assert len(g["ref_left"]) == g["flank"] + 1 and len(g["ref_right"]) == g["flank"] + 1
+        for seq, sp, (c0, c1), exp, exp_sp in zip(g["reads"], g["span"], g["ccoords"], g["out_reads"],
+                                                  g["out_span"]):
+            out, out_sp = seq, sp
+            if sp in (1, 2):
+                left = sp == 2 and c0 >= g["flank"]
+                right = sp == 1 and len(seq) - c1 >= g["flank"]
+                sub = seq[:c0] if left else (seq[c1:] if right else "")
+                if sub:
+                    cg = port_cigar(sub.encode(), (g["ref_left"] if left else g["ref_right"]).encode(),
+                                    0, 0, 0, 0, 0)[1]
+                    scores, j = [0] * len(sub), 0
+                    for op in cg:
+                        if op == "I":
+                            continue
+                        if op == "M":
+                            scores[j] = 1 if j == 0 else scores[j - 1] + 1
+                        elif j > 0 and scores[j - 1] > 0:
+                            scores[j] = scores[j - 1] - 1
+                        j += 1
+                    best = max(range(len(scores)), key=lambda i: (scores[i], -i))
+                    start_i = best
+                    while start_i > 0 and scores[start_i] > 0:
+                        start_i -= 1
+                    if scores[best] / float(g["flank"]) >= g["min_sim"]:
+                        out = seq[best:] if left else seq[:c1 + start_i]
+                        out_sp = 3
+            assert (out, out_sp) == (exp, exp_sp)
