@@ -116,7 +116,7 @@ int otgpu_batch_align(otgpu_ctx* ctx);
 int otgpu_batch_download(otgpu_ctx* ctx, int32_t* scores_out, uint64_t n_scores);
 int otgpu_synchronize(otgpu_ctx* ctx);
 /* Device time (CUDA events on ctx's stream) of the last otgpu_batch_align, per stage:
- * ms[0] pack, ms[1] pair expansion, ms[2] k_align (shared-memory wavefronts, the dominant
+ * ms[0] pack, ms[1] pair expansion + work ordering, ms[2] k_align (shared-memory wavefronts, the dominant
  * kernel), ms[3] k_align wide fallback.  Waits for that align to finish. */
 int otgpu_last_align_ms(otgpu_ctx* ctx, float ms[4]);
 

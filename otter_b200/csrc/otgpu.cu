@@ -91,26 +91,73 @@ __global__ void __launch_bounds__(128) k_expand_regions(const uint32_t* __restri
   }
 }
 
+// ---- heaviest-first work order -------------------------------------------------------------------
+// Pairs differ by 3-4 orders of magnitude in work.  The persistent warps
+// pull pairs from one queue, so the pairs are queued by descending estimated work (64 log-scale
+// buckets of |len difference| + len/16) to keep the tail of the launch short.
+constexpr int kBuckets = 64;
+struct OrderCtl { unsigned int hist[kBuckets]; unsigned int cursor[kBuckets]; };
+
+__device__ __forceinline__ int work_bucket(const otgpu_pair& p, const uint32_t* __restrict__ read_len) {
+  if (p.pattern == kEmptySlot) return 0;
+  const uint32_t a = read_len[p.pattern], b = read_len[p.text];
+  const uint32_t est = (a > b ? a - b : b - a) + (max(a, b) >> 4) + 1;
+  const int lg = 31 - __clz(est);                       // 0..31
+  const int half = lg > 0 ? (est >> (lg - 1)) & 1 : 0;  // one more bit of resolution
+  return min(kBuckets - 1, 2 * lg + half);
+}
+
+__global__ void __launch_bounds__(256) k_order_count(const otgpu_pair* __restrict__ pairs, uint64_t n,
+                                                     const uint32_t* __restrict__ read_len,
+                                                     OrderCtl* __restrict__ ctl) {
+  __shared__ unsigned int h[kBuckets];
+  if (threadIdx.x < kBuckets) h[threadIdx.x] = 0;
+  __syncthreads();
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    atomicAdd(&h[work_bucket(pairs[i], read_len)], 1u);
+  __syncthreads();
+  if (threadIdx.x < kBuckets && h[threadIdx.x]) atomicAdd(&ctl->hist[threadIdx.x], h[threadIdx.x]);
+}
+
+__global__ void k_order_scan(OrderCtl* __restrict__ ctl) {  // heaviest bucket first
+  unsigned int run = 0;
+  for (int b = kBuckets - 1; b >= 0; --b) {
+    ctl->cursor[b] = run;
+    run += ctl->hist[b];
+  }
+}
+
+__global__ void __launch_bounds__(256) k_order_scatter(const otgpu_pair* __restrict__ pairs, uint64_t n,
+                                                       const uint32_t* __restrict__ read_len,
+                                                       OrderCtl* __restrict__ ctl,
+                                                       uint32_t* __restrict__ order) {
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+    order[atomicAdd(&ctl->cursor[work_bucket(pairs[i], read_len)], 1u)] = (uint32_t)i;
+}
+
 __device__ __forceinline__ SeqView view2(const DevBatch& b, uint32_t r) {
-  return SeqView{(uint32_t)b.pk_off[r], 0};
+  return SeqView{b.packed + b.pk_off[r], 0};
 }
 __device__ __forceinline__ SeqView view8(const DevBatch& b, uint32_t r) {
   const uint64_t o = b.read_off[r];
-  return SeqView{(uint32_t)(o >> 2), (int)(o & 3ull)};
+  return SeqView{reinterpret_cast<const uint32_t*>(b.bases) + (o >> 2), (int)(o & 3ull)};
 }
 
 template <bool WIDE>
 __global__ void __launch_bounds__(kCtaThreads, 4)
-k_align(DevBatch b, Counters* __restrict__ ctr, uint32_t* __restrict__ ovf_list,
-        int32_t* __restrict__ wide_ws, int wide_cap) {
-  __shared__ int32_t ring_smem[WIDE ? 1 : kWarpsPerCta * kRingCap];
+k_align(DevBatch b, Counters* __restrict__ ctr, const uint32_t* __restrict__ order,
+        uint32_t* __restrict__ ovf_list, int32_t* __restrict__ wide_ws, int wide_cap) {
+  // one extra ring of slack: the rings are aligned to their size at run time (Ring<false>::addr
+  // ORs the slot offset into the base), whatever offset the static allocation starts at
+  __shared__ int32_t ring_smem[WIDE ? 1 : (kWarpsPerCta + 1) * kRingCap];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   Ring<WIDE> ring;
   if constexpr (WIDE) {
     ring.p = wide_ws + (size_t)(blockIdx.x * kWarpsPerCta + warp) * wide_cap;
     ring.mask = wide_cap - 1;
   } else {
-    ring.base = (unsigned)__cvta_generic_to_shared(ring_smem + warp * kRingCap);
+    const unsigned a0 = ((unsigned)__cvta_generic_to_shared(ring_smem) + kRingCap * 4 - 1) & ~(kRingCap * 4 - 1u);
+    ring.base = a0 + warp * (kRingCap * 4);
   }
   const unsigned long long limit = WIDE ? ctr->v[1] : b.n_pairs;
   for (;;) {
@@ -118,7 +165,7 @@ k_align(DevBatch b, Counters* __restrict__ ctr, uint32_t* __restrict__ ovf_list,
     if (lane == 0) q = atomicAdd(&ctr->v[WIDE ? 2 : 0], 1ull);
     q = __shfl_sync(kFull, q, 0);
     if (q >= limit) break;
-    const uint64_t idx = WIDE ? ovf_list[q] : q;
+    const uint64_t idx = WIDE ? ovf_list[q] : order[q];
     const otgpu_pair pr = b.pairs[idx];
     if (pr.pattern == kEmptySlot) {
       if (lane == 0) b.scores[idx] = 0;
@@ -132,12 +179,10 @@ k_align(DevBatch b, Counters* __restrict__ ctr, uint32_t* __restrict__ ovf_list,
     const bool bytes = ((b.read_flag[pr.pattern] | b.read_flag[pr.text]) & 1u) != 0;
     int score;
     if (bytes) {
-      J.words = reinterpret_cast<const uint32_t*>(b.bases);
       J.P = view8(b, pr.pattern); J.T = view8(b, pr.text);
       score = wfa_edit_pair<8, WIDE>(ring, J, lane);
       if (!WIDE && lane == 0) atomicAdd(&ctr->v[3], 1ull);
     } else {
-      J.words = b.packed;
       J.P = view2(b, pr.pattern); J.T = view2(b, pr.text);
       score = wfa_edit_pair<2, WIDE>(ring, J, lane);
     }
@@ -167,7 +212,7 @@ struct otgpu_ctx {
   cudaStream_t stream = nullptr;
   char err[256] = {0};
   DevBuf bases, read_off, read_len, pk_off, read_flag, packed, region_start, score_off, pairs,
-      scores, ovf_list, counters, wide_ws;
+      scores, ovf_list, counters, wide_ws, order, order_ctl;
   DevBuf aff_rings, aff_slab, aff_slab2, aff_ops, cigar_off, cigars, cigar_len;  // gap-affine path
   void* h_pk_off = nullptr;  // pinned
   size_t h_pk_off_cap = 0;
@@ -230,10 +275,6 @@ int upload_reads(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const u
     size_t want = (size_t)n_reads * 8 + (size_t)n_reads + 4096;
     CK(cudaMallocHost(&ctx->h_pk_off, want));
     ctx->h_pk_off_cap = want;
-  }
-  if (n_bases >= ((uint64_t)1 << 34)) {  // kernels address reads by 32-bit word index
-    snprintf(ctx->err, sizeof(ctx->err), "batch exceeds 16 GiB of bases; split it");
-    return OTGPU_ERR_ARGS;
   }
   uint64_t* pk = static_cast<uint64_t*>(ctx->h_pk_off);
   uint64_t words = 0;
@@ -338,7 +379,7 @@ void otgpu_destroy(otgpu_ctx* ctx) {
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   DevBuf* bufs[] = {&ctx->bases, &ctx->read_off, &ctx->read_len, &ctx->pk_off, &ctx->read_flag,
                     &ctx->packed, &ctx->region_start, &ctx->score_off, &ctx->pairs, &ctx->scores,
-                    &ctx->ovf_list, &ctx->counters, &ctx->wide_ws, &ctx->aff_rings,
+                    &ctx->ovf_list, &ctx->counters, &ctx->wide_ws, &ctx->order, &ctx->order_ctl, &ctx->aff_rings,
                     &ctx->aff_slab, &ctx->aff_slab2, &ctx->aff_ops, &ctx->cigar_off, &ctx->cigars,
                     &ctx->cigar_len};
   for (DevBuf* b : bufs)
@@ -394,6 +435,8 @@ int otgpu_batch_upload_regions(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_
   RS(pairs, (size_t)n_scores * sizeof(otgpu_pair) + 32);
   RS(scores, (size_t)n_scores * 4 + 4);
   RS(ovf_list, (size_t)n_scores * 4 + 4);
+  RS(order, (size_t)n_scores * 4 + 4);
+  RS(order_ctl, sizeof(OrderCtl));
   CK(cudaMemcpyAsync(ctx->region_start.p, region_start, (size_t)(n_regions + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
   if (n_regions)
     CK(cudaMemcpyAsync(ctx->score_off.p, score_off, (size_t)n_regions * 8, cudaMemcpyHostToDevice, ctx->stream));
@@ -430,6 +473,8 @@ int otgpu_batch_upload_pairs(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_ba
   RS(pairs, (size_t)n_pairs * sizeof(otgpu_pair) + 32);
   RS(scores, (size_t)n_pairs * 4 + 4);
   RS(ovf_list, (size_t)n_pairs * 4 + 4);
+  RS(order, (size_t)n_pairs * 4 + 4);
+  RS(order_ctl, sizeof(OrderCtl));
   if (n_pairs)
     CK(cudaMemcpyAsync(ctx->pairs.p, pairs, (size_t)n_pairs * sizeof(otgpu_pair), cudaMemcpyHostToDevice, ctx->stream));
   ctx->n_pairs = n_pairs;
@@ -475,14 +520,26 @@ int otgpu_batch_align(otgpu_ctx* ctx) {
       ctx->stats.kernel_launches++;
     }
   }
+  if (ctx->n_pairs) {  // heaviest-first queue order
+    OrderCtl* ctl = static_cast<OrderCtl*>(ctx->order_ctl.p);
+    CK(cudaMemsetAsync(ctl, 0, sizeof(OrderCtl), st));
+    const int g = (int)((ctx->n_pairs + 255) / 256 < (uint64_t)ctx->n_sm * 8 ? (ctx->n_pairs + 255) / 256
+                                                                             : (uint64_t)ctx->n_sm * 8);
+    k_order_count<<<g, 256, 0, st>>>(b.pairs, ctx->n_pairs, b.read_len, ctl);
+    k_order_scan<<<1, 1, 0, st>>>(ctl);
+    k_order_scatter<<<g, 256, 0, st>>>(b.pairs, ctx->n_pairs, b.read_len, ctl,
+                                       static_cast<uint32_t*>(ctx->order.p));
+    ctx->stats.kernel_launches += 3;
+  }
   CK(cudaEventRecord(ctx->ev[2], st));
   if (ctx->n_pairs) {
     Counters* ctr = static_cast<Counters*>(ctx->counters.p);
     uint32_t* ovf = static_cast<uint32_t*>(ctx->ovf_list.p);
-    k_align<false><<<ctx->grid_main, kCtaThreads, 0, st>>>(b, ctr, ovf, nullptr, 0);
+    uint32_t* order = static_cast<uint32_t*>(ctx->order.p);
+    k_align<false><<<ctx->grid_main, kCtaThreads, 0, st>>>(b, ctr, order, ovf, nullptr, 0);
     CK(cudaEventRecord(ctx->ev[3], st));
     k_align<true><<<ctx->grid_wide, kCtaThreads, 0, st>>>(
-        b, ctr, ovf, static_cast<int32_t*>(ctx->wide_ws.p), ctx->wide_cap);
+        b, ctr, order, ovf, static_cast<int32_t*>(ctx->wide_ws.p), ctx->wide_cap);
     ctx->stats.kernel_launches += 2;
   } else {
     CK(cudaEventRecord(ctx->ev[3], st));
@@ -584,11 +641,9 @@ k_affine(DevBatch b, Counters* __restrict__ ctr, uint32_t* __restrict__ ovf_list
     const int cap = (int)(cigar_off[idx + 1] - c0);
     int score = 0, len;
     if (bytes) {
-      J.words = reinterpret_cast<const uint32_t*>(b.bases);
       J.P = view8(b, pr.pattern); J.T = view8(b, pr.text);
       len = wfa_affine_pair<8>(W, meta_smem[warp], J, pen, lane, cigars + c0, cap, &score);
     } else {
-      J.words = b.packed;
       J.P = view2(b, pr.pattern); J.T = view2(b, pr.text);
       len = wfa_affine_pair<2>(W, meta_smem[warp], J, pen, lane, cigars + c0, cap, &score);
     }

@@ -52,7 +52,7 @@ __device__ __forceinline__ int lcp_uniform(const EditJob& J, int v, int h, int r
     int mm = 0;
     bool stop = true;
     if (o < rem) {
-      mm = match_window<BITS>(J.words, J.P, J.T, v + o, h + o);
+      mm = match_window<BITS>(J.P, J.T, v + o, h + o);
       const int lim = rem - o;
       if (mm >= lim) mm = lim;
       else stop = mm < WIN;

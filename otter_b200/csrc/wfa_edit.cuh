@@ -36,7 +36,7 @@ constexpr int kMaxDist = 50;    // wavefront_attributes.c:75
 constexpr int kPruneLen = 1000; // wavefront_compute_edit.c:224
 constexpr int kScoreOverflow = -2;  // internal: live width exceeded the shared-memory ring
 constexpr int kBigDist = 1 << 30;   // distance of a null offset, wavefront_heuristic.c:118
-constexpr int kRingCap = 512;       // int32 slots per warp in shared memory
+constexpr int kRingCap = 1024;      // int32 slots per warp in shared memory (4 KiB, 4 KiB aligned)
 
 // ---- wavefront ring ---------------------------------------------------------------------------
 __device__ __forceinline__ int lds32(unsigned a) {
@@ -52,11 +52,12 @@ template <bool WIDE>
 struct Ring;
 template <>
 struct Ring<false> {  // shared memory, fixed capacity, 32-bit shared-window addressing
-  unsigned base;
+  unsigned base;      // aligned to the ring size, so slot address = base | ((k*4) & mask): one LOP3
   static constexpr unsigned kMaskB = (kRingCap - 1) * 4;
   __device__ __forceinline__ int cap() const { return kRingCap; }
-  __device__ __forceinline__ int ld(int k) const { return lds32(base + (((unsigned)k << 2) & kMaskB)); }
-  __device__ __forceinline__ void st(int k, int v) const { sts32(base + (((unsigned)k << 2) & kMaskB), v); }
+  __device__ __forceinline__ unsigned addr(int k) const { return base | (((unsigned)k << 2) & kMaskB); }
+  __device__ __forceinline__ int ld(int k) const { return lds32(addr(k)); }
+  __device__ __forceinline__ void st(int k, int v) const { sts32(addr(k), v); }
 };
 template <>
 struct Ring<true> {  // HBM workspace (L1/L2 cached), capacity covers every diagonal of the pair
@@ -68,10 +69,10 @@ struct Ring<true> {  // HBM workspace (L1/L2 cached), capacity covers every diag
 };
 
 // ---- packed reads -----------------------------------------------------------------------------
-// A read as the kernel sees it: 32-bit word index of its first word inside the batch buffer
-// (2-bit words, or the raw byte buffer viewed as words) + position of base 0 inside that word.
+// A read as the kernel sees it: pointer to its first word (2-bit words, or the raw byte buffer
+// viewed as words) + position of base 0 inside that word.
 struct SeqView {
-  uint32_t word0;
+  const uint32_t* __restrict__ w;  // first word of the read
   int sh0;  // always 0 for 2-bit reads (16-byte aligned); 0..3 for raw bytes
 };
 
@@ -87,10 +88,9 @@ struct Pack {
 // funnel shifts (shf.wrap takes the shift modulo 32, so no masking of the bit offset).
 // Touches up to two words past the word holding p; buffers carry guards for that.
 template <int BITS>
-__device__ __forceinline__ void window64(const uint32_t* __restrict__ words, const SeqView& s,
-                                         int p, uint32_t& lo, uint32_t& hi) {
+__device__ __forceinline__ void window64(const SeqView& s, int p, uint32_t& lo, uint32_t& hi) {
   const int a = (BITS == 2) ? p : s.sh0 + p;
-  const uint32_t* q = words + (s.word0 + (uint32_t)(a >> Pack<BITS>::kLogBpw));
+  const uint32_t* q = s.w + (a >> Pack<BITS>::kLogBpw);
   const uint32_t w0 = __ldg(q), w1 = __ldg(q + 1), w2 = __ldg(q + 2);
   const int sh = a << Pack<BITS>::kLogBits;
   lo = __funnelshift_r(w0, w1, sh);
@@ -99,11 +99,10 @@ __device__ __forceinline__ void window64(const uint32_t* __restrict__ words, con
 
 // Matching bases at the front of P[v..] and T[h..] within one 64-bit window (kWin if identical).
 template <int BITS>
-__device__ __forceinline__ int match_window(const uint32_t* __restrict__ words, const SeqView& P,
-                                            const SeqView& T, int v, int h) {
+__device__ __forceinline__ int match_window(const SeqView& P, const SeqView& T, int v, int h) {
   uint32_t pl, ph, tl, th;
-  window64<BITS>(words, P, v, pl, ph);
-  window64<BITS>(words, T, h, tl, th);
+  window64<BITS>(P, v, pl, ph);
+  window64<BITS>(T, h, tl, th);
   const uint32_t xl = pl ^ tl, xh = ph ^ th;
   const uint32_t sel = xl ? xl : xh;
   const int bit = (__ffs(sel) - 1) + (xl ? 0 : 32);
@@ -111,7 +110,6 @@ __device__ __forceinline__ int match_window(const uint32_t* __restrict__ words, 
 }
 
 struct EditJob {
-  const uint32_t* __restrict__ words;  // packed 2-bit words, or the raw bytes viewed as words
   SeqView P, T;
   int plen, tlen;
   int pb, pe, tb, te;  // pb < 0 => end-to-end
@@ -124,7 +122,7 @@ struct EditJob {
 template <int BITS>
 __device__ __forceinline__ int lcp_warp(const EditJob& J, int v, int h, int rem, const int lane) {
   constexpr int WIN = Pack<BITS>::kWin;
-  int m = match_window<BITS>(J.words, J.P, J.T, v, h);
+  int m = match_window<BITS>(J.P, J.T, v, h);
   int n = max(min(m, rem), 0);  // clamp at a sequence end (the reference stops on its sentinels)
   bool cont = (m >= WIN) && (rem > WIN);
   unsigned pend = __ballot_sync(kFull, cont);
@@ -132,7 +130,7 @@ __device__ __forceinline__ int lcp_warp(const EditJob& J, int v, int h, int rem,
   for (int it = 0;; ++it) {
     if (cont) {
       v += WIN; h += WIN; rem -= WIN;
-      m = match_window<BITS>(J.words, J.P, J.T, v, h);
+      m = match_window<BITS>(J.P, J.T, v, h);
       n += min(m, rem);
       cont = (m >= WIN) && (rem > WIN);
     }
@@ -152,7 +150,7 @@ __device__ __forceinline__ int lcp_warp(const EditJob& J, int v, int h, int rem,
       int mm = 0;
       bool stop = true;
       if (o < brem) {
-        mm = match_window<BITS>(J.words, J.P, J.T, bv + o, bh + o);
+        mm = match_window<BITS>(J.P, J.T, bv + o, bh + o);
         const int lim = brem - o;
         if (mm >= lim) mm = lim;
         else stop = mm < WIN;
