@@ -269,4 +269,32 @@ int ref_assemble_region(const char* bases, const uint64_t* off, const uint32_t* 
   for (uint32_t i = 0; i < n_reads; ++i) out_labels[i] = labels[i];
   return clust.fc;
 }
+
+// aligner2 over a list of (pattern, text, pb, pe, tb, te) requests (pb < 0: end-to-end), static
+// contiguous blocks over `threads` workers, one WFAlignerGapAffine(4,6,2,Alignment,MemoryMed)
+// each.  pairs = 6 int32 per request (pattern read, text read, pb, pe, tb, te).  Returns wall
+// seconds; cigar_len[i] = length of request i's CIGAR (the strings themselves are dropped).
+double ref_affine_cigars_batch(const char* bases, const uint64_t* off, const uint32_t* len,
+                               const int32_t* pairs, uint64_t n_pairs, int threads,
+                               int32_t* cigar_len) {
+  if (threads < 1) threads = 1;
+  auto t0 = std::chrono::steady_clock::now();
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; ++t) {
+    pool.emplace_back([&, t]() {
+      wfa::WFAlignerGapAffine a(4, 6, 2, wfa::WFAligner::Alignment, wfa::WFAligner::MemoryMed);
+      const uint64_t lo = n_pairs * t / threads, hi = n_pairs * (t + 1) / threads;
+      for (uint64_t i = lo; i < hi; ++i) {
+        const int32_t* q = pairs + 6 * i;
+        const char* p = bases + off[q[0]];
+        const char* x = bases + off[q[1]];
+        if (q[2] < 0) a.alignEnd2End(p, (int)len[q[0]], x, (int)len[q[1]]);
+        else a.alignEndsFree(p, (int)len[q[0]], q[2], q[3], x, (int)len[q[1]], q[4], q[5]);
+        cigar_len[i] = (int32_t)a.getAlignmentCigar().size();
+      }
+    });
+  }
+  for (auto& th : pool) th.join();
+  return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
 }

@@ -4,7 +4,8 @@ import os
 
 import numpy as np
 
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libotter_b200.so")
+LIB_PATH = os.environ.get("OTTER_B200_LIB") or os.path.join(
+    os.path.dirname(os.path.abspath(__file__)), "lib", "libotter_b200.so")  # env: kernel experiments
 
 # Every symbol include/otter_b200.h declares; tests assert the library exports all of them.
 SYMBOLS = [

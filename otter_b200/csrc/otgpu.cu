@@ -136,15 +136,18 @@ __global__ void __launch_bounds__(256) k_order_scatter(const otgpu_pair* __restr
 }
 
 __device__ __forceinline__ SeqView view2(const DevBatch& b, uint32_t r) {
-  return SeqView{b.packed + b.pk_off[r], 0};
+  return SeqView{(uint32_t)b.pk_off[r], 0};
 }
 __device__ __forceinline__ SeqView view8(const DevBatch& b, uint32_t r) {
   const uint64_t o = b.read_off[r];
-  return SeqView{reinterpret_cast<const uint32_t*>(b.bases) + (o >> 2), (int)(o & 3ull)};
+  return SeqView{(uint32_t)(o >> 2), (int)(o & 3ull)};
 }
 
+#ifndef OTGPU_ALIGN_MIN_CTAS
+#define OTGPU_ALIGN_MIN_CTAS 4
+#endif
 template <bool WIDE>
-__global__ void __launch_bounds__(kCtaThreads, 4)
+__global__ void __launch_bounds__(kCtaThreads, OTGPU_ALIGN_MIN_CTAS)
 k_align(DevBatch b, Counters* __restrict__ ctr, const uint32_t* __restrict__ order,
         uint32_t* __restrict__ ovf_list, int32_t* __restrict__ wide_ws, int wide_cap) {
   // one extra ring of slack: the rings are aligned to their size at run time (Ring<false>::addr
@@ -179,10 +182,12 @@ k_align(DevBatch b, Counters* __restrict__ ctr, const uint32_t* __restrict__ ord
     const bool bytes = ((b.read_flag[pr.pattern] | b.read_flag[pr.text]) & 1u) != 0;
     int score;
     if (bytes) {
+      J.words = reinterpret_cast<const uint32_t*>(b.bases);
       J.P = view8(b, pr.pattern); J.T = view8(b, pr.text);
       score = wfa_edit_pair<8, WIDE>(ring, J, lane);
       if (!WIDE && lane == 0) atomicAdd(&ctr->v[3], 1ull);
     } else {
+      J.words = b.packed;
       J.P = view2(b, pr.pattern); J.T = view2(b, pr.text);
       score = wfa_edit_pair<2, WIDE>(ring, J, lane);
     }
@@ -275,6 +280,10 @@ int upload_reads(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const u
     size_t want = (size_t)n_reads * 8 + (size_t)n_reads + 4096;
     CK(cudaMallocHost(&ctx->h_pk_off, want));
     ctx->h_pk_off_cap = want;
+  }
+  if (n_bases >= ((uint64_t)1 << 34)) {  // kernels address reads by 32-bit word index
+    snprintf(ctx->err, sizeof(ctx->err), "batch exceeds 16 GiB of bases; split it");
+    return OTGPU_ERR_ARGS;
   }
   uint64_t* pk = static_cast<uint64_t*>(ctx->h_pk_off);
   uint64_t words = 0;
@@ -641,9 +650,11 @@ k_affine(DevBatch b, Counters* __restrict__ ctr, uint32_t* __restrict__ ovf_list
     const int cap = (int)(cigar_off[idx + 1] - c0);
     int score = 0, len;
     if (bytes) {
+      J.words = reinterpret_cast<const uint32_t*>(b.bases);
       J.P = view8(b, pr.pattern); J.T = view8(b, pr.text);
       len = wfa_affine_pair<8>(W, meta_smem[warp], J, pen, lane, cigars + c0, cap, &score);
     } else {
+      J.words = b.packed;
       J.P = view2(b, pr.pattern); J.T = view2(b, pr.text);
       len = wfa_affine_pair<2>(W, meta_smem[warp], J, pen, lane, cigars + c0, cap, &score);
     }

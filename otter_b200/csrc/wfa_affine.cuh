@@ -52,7 +52,7 @@ __device__ __forceinline__ int lcp_uniform(const EditJob& J, int v, int h, int r
     int mm = 0;
     bool stop = true;
     if (o < rem) {
-      mm = match_window<BITS>(J.P, J.T, v + o, h + o);
+      mm = match_window<BITS>(J.words, J.P, J.T, v + o, h + o);
       const int lim = rem - o;
       if (mm >= lim) mm = lim;
       else stop = mm < WIN;
@@ -130,7 +130,7 @@ __device__ int wfa_affine_pair(const AffWork& W, AffSlot* __restrict__ meta, con
         const bool live = off >= 0;  // M offsets are in-bounds or exactly NULL
         const int v = off - k;
         const int rem = live ? min(plen - v, tlen - off) : 0;
-        off += lcp_warp<BITS>(J, live ? v : 0, live ? off : 0, rem, lane);
+        off += lcp_warp<BITS>(J, v, off, rem, lane);
         bool term = false;
         if (live) {
           m[k & mask] = off;

@@ -69,10 +69,12 @@ struct Ring<true> {  // HBM workspace (L1/L2 cached), capacity covers every diag
 };
 
 // ---- packed reads -----------------------------------------------------------------------------
-// A read as the kernel sees it: pointer to its first word (2-bit words, or the raw byte buffer
-// viewed as words) + position of base 0 inside that word.
+// A read as the kernel sees it: 32-bit word index of its first word inside the batch buffer
+// (2-bit words, or the raw byte buffer viewed as words) + position of base 0 inside that word.
+// (Index + one warp-uniform base pointer costs two instructions per window address, LEA.HI +
+// IMAD.WIDE; a per-read 64-bit pointer costs five.)
 struct SeqView {
-  const uint32_t* __restrict__ w;  // first word of the read
+  uint32_t word0;
   int sh0;  // always 0 for 2-bit reads (16-byte aligned); 0..3 for raw bytes
 };
 
@@ -88,10 +90,12 @@ struct Pack {
 // funnel shifts (shf.wrap takes the shift modulo 32, so no masking of the bit offset).
 // Touches up to two words past the word holding p; buffers carry guards for that.
 template <int BITS>
-__device__ __forceinline__ void window64(const SeqView& s, int p, uint32_t& lo, uint32_t& hi) {
+__device__ __forceinline__ void window64(const uint32_t* __restrict__ words, const SeqView& s,
+                                         int p, bool on, uint32_t& lo, uint32_t& hi) {
   const int a = (BITS == 2) ? p : s.sh0 + p;
-  const uint32_t* q = s.w + (a >> Pack<BITS>::kLogBpw);
-  const uint32_t w0 = __ldg(q), w1 = __ldg(q + 1), w2 = __ldg(q + 2);
+  const uint32_t* q = words + (s.word0 + (uint32_t)(a >> Pack<BITS>::kLogBpw));
+  uint32_t w0 = 0, w1 = 0, w2 = 0;
+  if (on) { w0 = __ldg(q); w1 = __ldg(q + 1); w2 = __ldg(q + 2); }  // predicated loads
   const int sh = a << Pack<BITS>::kLogBits;
   lo = __funnelshift_r(w0, w1, sh);
   hi = __funnelshift_r(w1, w2, sh);
@@ -99,10 +103,11 @@ __device__ __forceinline__ void window64(const SeqView& s, int p, uint32_t& lo, 
 
 // Matching bases at the front of P[v..] and T[h..] within one 64-bit window (kWin if identical).
 template <int BITS>
-__device__ __forceinline__ int match_window(const SeqView& P, const SeqView& T, int v, int h) {
+__device__ __forceinline__ int match_window(const uint32_t* __restrict__ words, const SeqView& P,
+                                            const SeqView& T, int v, int h, bool on = true) {
   uint32_t pl, ph, tl, th;
-  window64<BITS>(P, v, pl, ph);
-  window64<BITS>(T, h, tl, th);
+  window64<BITS>(words, P, v, on, pl, ph);
+  window64<BITS>(words, T, h, on, tl, th);
   const uint32_t xl = pl ^ tl, xh = ph ^ th;
   const uint32_t sel = xl ? xl : xh;
   const int bit = (__ffs(sel) - 1) + (xl ? 0 : 32);
@@ -110,19 +115,20 @@ __device__ __forceinline__ int match_window(const SeqView& P, const SeqView& T, 
 }
 
 struct EditJob {
+  const uint32_t* __restrict__ words;  // packed 2-bit words, or the raw bytes viewed as words
   SeqView P, T;
   int plen, tlen;
   int pb, pe, tb, te;  // pb < 0 => end-to-end
 };
 
 // Longest common prefix of P[v..v+rem) and T[h..h+rem) for every lane at once (rem <= 0 for lanes
-// with nothing to extend; their v/h must still be loadable).  All 32 lanes must call.
+// with nothing to extend: they issue no loads).  All 32 lanes must call.
 // First window is unconditional; after that, private windows while several lanes are still
 // running, and once at most two are left each remaining run is finished by the whole warp.
 template <int BITS>
 __device__ __forceinline__ int lcp_warp(const EditJob& J, int v, int h, int rem, const int lane) {
   constexpr int WIN = Pack<BITS>::kWin;
-  int m = match_window<BITS>(J.P, J.T, v, h);
+  int m = match_window<BITS>(J.words, J.P, J.T, v, h, rem > 0);
   int n = max(min(m, rem), 0);  // clamp at a sequence end (the reference stops on its sentinels)
   bool cont = (m >= WIN) && (rem > WIN);
   unsigned pend = __ballot_sync(kFull, cont);
@@ -130,7 +136,7 @@ __device__ __forceinline__ int lcp_warp(const EditJob& J, int v, int h, int rem,
   for (int it = 0;; ++it) {
     if (cont) {
       v += WIN; h += WIN; rem -= WIN;
-      m = match_window<BITS>(J.P, J.T, v, h);
+      m = match_window<BITS>(J.words, J.P, J.T, v, h);
       n += min(m, rem);
       cont = (m >= WIN) && (rem > WIN);
     }
@@ -150,7 +156,7 @@ __device__ __forceinline__ int lcp_warp(const EditJob& J, int v, int h, int rem,
       int mm = 0;
       bool stop = true;
       if (o < brem) {
-        mm = match_window<BITS>(J.P, J.T, bv + o, bh + o);
+        mm = match_window<BITS>(J.words, J.P, J.T, bv + o, bh + o);
         const int lim = brem - o;
         if (mm >= lim) mm = lim;
         else stop = mm < WIN;
@@ -197,6 +203,9 @@ __device__ __forceinline__ void wf_pass(const Ring<WIDE>& R, const EditJob& J, c
   int k = clo + lane;
   int mid = R.ld(k);
   if ((unsigned)(k - lo) > span) mid = kNull;
+#ifdef OTGPU_UNROLL2
+#pragma unroll 2
+#endif
   for (int kc = clo; kc <= chi; kc += 32, k += 32) {
     int m, nxt = R.ld(k + 32);  // this lane's slot in the next chunk (still old)
     if ((unsigned)(k + 32 - lo) > span) nxt = kNull;
@@ -219,7 +228,7 @@ __device__ __forceinline__ void wf_pass(const Ring<WIDE>& R, const EditJob& J, c
     const int rem = min(plen - v, tlen - m);
     const bool ok = (m | v | rem) >= 0;
     if (EXTEND) {
-      m += lcp_warp<BITS>(J, ok ? v : 0, ok ? m : 0, ok ? rem : 0, lane);
+      m += lcp_warp<BITS>(J, v, m, ok ? rem : 0, lane);
       if (ok) {
         dmin = min(dmin, plen + max(k, ak) - m);  // = max(plen - v', tlen - m')
         if (EF) {
