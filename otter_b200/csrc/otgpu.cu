@@ -27,7 +27,7 @@ constexpr int kCtaThreads = kWarpsPerCta * 32;
 constexpr uint32_t kEmptySlot = 0xffffffffu;
 
 struct DevBatch {
-  const uint8_t* bases;      // raw bytes (+16 B slack)
+  const uint8_t* bases;      // raw bytes, preceded and followed by kPadBases guard bytes
   const uint64_t* read_off;  // byte offset of each read in bases
   const uint32_t* read_len;
   const uint64_t* pk_off;    // word offset of each read in packed
@@ -45,7 +45,7 @@ struct Counters { unsigned long long v[4]; };
 __global__ void __launch_bounds__(128) k_pack_reads(DevBatch b, uint32_t* __restrict__ packed) {
   const uint32_t r = blockIdx.x;
   const uint32_t len = b.read_len[r];
-  const uint8_t* __restrict__ src = b.bases + b.read_off[r];
+  const uint8_t* __restrict__ src = b.bases + kPadBases + b.read_off[r];
   uint32_t* __restrict__ dst = packed + b.pk_off[r];
   const uint32_t nwords = (len + 15) / 16 + 2;  // + guard words the window loads may touch
   bool bad = false;
@@ -139,7 +139,7 @@ __device__ __forceinline__ SeqView view2(const DevBatch& b, uint32_t r) {
   return SeqView{(uint32_t)b.pk_off[r], 0};
 }
 __device__ __forceinline__ SeqView view8(const DevBatch& b, uint32_t r) {
-  const uint64_t o = b.read_off[r];
+  const uint64_t o = b.read_off[r] + kPadBases;
   return SeqView{(uint32_t)(o >> 2), (int)(o & 3ull)};
 }
 
@@ -281,30 +281,38 @@ int upload_reads(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const u
     CK(cudaMallocHost(&ctx->h_pk_off, want));
     ctx->h_pk_off_cap = want;
   }
-  if (n_bases >= ((uint64_t)1 << 34)) {  // kernels address reads by 32-bit word index
+  if (n_bases + 2ull * kPadBases >= ((uint64_t)1 << 34)) {  // kernels address reads by 32-bit word index
     snprintf(ctx->err, sizeof(ctx->err), "batch exceeds 16 GiB of bases; split it");
     return OTGPU_ERR_ARGS;
   }
   uint64_t* pk = static_cast<uint64_t*>(ctx->h_pk_off);
-  uint64_t words = 0;
+  // guard words either side: the extension's window loads are unguarded and a null-derived
+  // offset addresses up to kPadBases positions before a read (wfa_edit.cuh)
+  uint64_t words = kPadBases / 16;
   uint32_t max_len = 0;
   for (uint32_t r = 0; r < n_reads; ++r) {
     if (read_off[r] + read_len[r] > n_bases) {
       snprintf(ctx->err, sizeof(ctx->err), "read %u exceeds the bases buffer", r);
       return OTGPU_ERR_ARGS;
     }
+    if (read_len[r] > kMaxReadLen) {
+      snprintf(ctx->err, sizeof(ctx->err), "read %u is longer than %u bases", r, kMaxReadLen);
+      return OTGPU_ERR_ARGS;
+    }
     pk[r] = words;
     words += (((uint64_t)read_len[r] + 15) / 16 + 2 + 3) & ~3ull;  // 16 B aligned, >= 2 guards
     if (read_len[r] > max_len) max_len = read_len[r];
   }
-  RS(bases, n_bases + 16);
+  RS(bases, n_bases + 2ull * kPadBases + 16);
   RS(read_off, (size_t)n_reads * 8 + 8);
   RS(read_len, (size_t)n_reads * 4 + 4);
   RS(pk_off, (size_t)n_reads * 8 + 8);
   RS(read_flag, (size_t)n_reads * 4 + 4);
-  RS(packed, (words + 4) * 4);
+  RS(packed, (words + kPadBases / 16 + 4) * 4);
   RS(counters, sizeof(Counters));
-  if (n_bases) CK(cudaMemcpyAsync(ctx->bases.p, bases, n_bases, cudaMemcpyHostToDevice, ctx->stream));
+  if (n_bases)
+    CK(cudaMemcpyAsync(static_cast<uint8_t*>(ctx->bases.p) + kPadBases, bases, n_bases,
+                       cudaMemcpyHostToDevice, ctx->stream));
   if (n_reads) {
     CK(cudaMemcpyAsync(ctx->read_off.p, read_off, (size_t)n_reads * 8, cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync(ctx->read_len.p, read_len, (size_t)n_reads * 4, cudaMemcpyHostToDevice, ctx->stream));
@@ -325,7 +333,7 @@ int size_launch(otgpu_ctx* ctx) {
     ctx->grid_main = ctx->n_sm * per_sm;
   }
   // wide fallback: ring must hold every diagonal of the longest possible pair
-  const int need = next_pow2(2 * (int)ctx->max_len + 64);
+  const int need = next_pow2(2 * (int)ctx->max_len + 256);
   int grid_wide = ctx->n_sm * 2;
   const size_t budget = (size_t)4 << 30;
   while (grid_wide > 1 && (size_t)grid_wide * kWarpsPerCta * need * 4 > budget) grid_wide /= 2;

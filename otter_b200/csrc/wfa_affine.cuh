@@ -41,32 +41,6 @@ struct AffWork {        // per-warp workspace in HBM
 
 struct AffPen { int x, o, e, scope; };
 
-// LCP of P[v..) and T[h..) for ONE warp-uniform position, all lanes cooperating (32 windows per
-// round).  rem = min(plen - v, tlen - h).
-template <int BITS>
-__device__ __forceinline__ int lcp_uniform(const EditJob& J, int v, int h, int rem, const int lane) {
-  constexpr int WIN = Pack<BITS>::kWin;
-  int got = 0;
-  while (rem > 0) {
-    const int o = lane * WIN;
-    int mm = 0;
-    bool stop = true;
-    if (o < rem) {
-      mm = match_window<BITS>(J.words, J.P, J.T, v + o, h + o);
-      const int lim = rem - o;
-      if (mm >= lim) mm = lim;
-      else stop = mm < WIN;
-    }
-    const unsigned b = __ballot_sync(kFull, stop);
-    if (b) {
-      const int f = __ffs(b) - 1;
-      return got + f * WIN + __shfl_sync(kFull, mm, f);
-    }
-    got += 32 * WIN; v += 32 * WIN; h += 32 * WIN; rem -= 32 * WIN;
-  }
-  return got;
-}
-
 __device__ __forceinline__ bool in_bounds(int off, int k, int plen, int tlen) {
   return (unsigned)off <= (unsigned)tlen && (unsigned)(off - k) <= (unsigned)plen;
 }

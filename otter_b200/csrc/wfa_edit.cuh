@@ -29,7 +29,15 @@
 
 namespace otgpu {
 
-constexpr int kNull = -(1 << 30);  // WAVEFRONT_OFFSET_NULL, wavefront_offset.h:46
+constexpr int kNull = -(1 << 30);  // WAVEFRONT_OFFSET_NULL, wavefront_offset.h:46 (gap-affine path)
+// Null offset of the EDIT path.  Only its sign and being out of bounds matter there (a stored
+// offset is either in bounds or exactly null; null + 1 is re-nulled by the same pass), so a
+// smaller magnitude is equivalent — and keeps the positions that null-derived offsets address
+// within a few MiB of the read, where the batch buffers are padded, so the extension's window
+// loads need no guards.
+constexpr int kENull = -(1 << 22);
+constexpr uint32_t kMaxReadLen = 1u << 20;                       // enforced at upload
+constexpr uint32_t kPadBases = (1u << 22) + 2 * kMaxReadLen + 4096;  // guard positions either side
 constexpr unsigned kFull = 0xffffffffu;
 constexpr int kMinWfLen = 10;   // wavefront_attributes.c:74
 constexpr int kMaxDist = 50;    // wavefront_attributes.c:75
@@ -58,6 +66,24 @@ struct Ring<false> {  // shared memory, fixed capacity, 32-bit shared-window add
   __device__ __forceinline__ unsigned addr(int k) const { return base | (((unsigned)k << 2) & kMaskB); }
   __device__ __forceinline__ int ld(int k) const { return lds32(addr(k)); }
   __device__ __forceinline__ void st(int k, int v) const { sts32(addr(k), v); }
+  // pair of adjacent slots (k even), addressed through a token so that a pass computes each
+  // address once (loaded as "next", stored one round later as "current")
+  typedef unsigned Tok;
+  __device__ __forceinline__ Tok tok(int k) const { return addr(k); }
+  __device__ __forceinline__ int2 ld2(Tok t) const {
+    int2 v;
+    asm volatile("ld.shared.v2.s32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(t) : "memory");
+    return v;
+  }
+  __device__ __forceinline__ void st2(Tok t, int a, int b) const {
+    asm volatile("st.shared.v2.s32 [%0], {%1, %2};" ::"r"(t), "r"(a), "r"(b) : "memory");
+  }
+  __device__ __forceinline__ void fill_null(int lane) const {
+#pragma unroll
+    for (int i = 0; i < kRingCap / 128; ++i)
+      asm volatile("st.shared.v4.s32 [%0], {%1, %1, %1, %1};" ::"r"(base + (i * 32 + lane) * 16), "r"(kENull)
+                   : "memory");
+  }
 };
 template <>
 struct Ring<true> {  // HBM workspace (L1/L2 cached), capacity covers every diagonal of the pair
@@ -66,6 +92,13 @@ struct Ring<true> {  // HBM workspace (L1/L2 cached), capacity covers every diag
   __device__ __forceinline__ int cap() const { return mask + 1; }
   __device__ __forceinline__ int ld(int k) const { return p[k & mask]; }
   __device__ __forceinline__ void st(int k, int v) const { p[k & mask] = v; }
+  typedef int2* Tok;
+  __device__ __forceinline__ Tok tok(int k) const { return reinterpret_cast<int2*>(p + (k & mask)); }
+  __device__ __forceinline__ int2 ld2(Tok t) const { return *t; }
+  __device__ __forceinline__ void st2(Tok t, int a, int b) const { *t = make_int2(a, b); }
+  __device__ __forceinline__ void fill_null(int lane) const {
+    for (int i = lane; i <= mask; i += 32) p[i] = kENull;
+  }
 };
 
 // ---- packed reads -----------------------------------------------------------------------------
@@ -91,27 +124,28 @@ struct Pack {
 // Touches up to two words past the word holding p; buffers carry guards for that.
 template <int BITS>
 __device__ __forceinline__ void window64(const uint32_t* __restrict__ words, const SeqView& s,
-                                         int p, bool on, uint32_t& lo, uint32_t& hi) {
+                                         int p, uint32_t& lo, uint32_t& hi) {
   const int a = (BITS == 2) ? p : s.sh0 + p;
   const uint32_t* q = words + (s.word0 + (uint32_t)(a >> Pack<BITS>::kLogBpw));
-  uint32_t w0 = 0, w1 = 0, w2 = 0;
-  if (on) { w0 = __ldg(q); w1 = __ldg(q + 1); w2 = __ldg(q + 2); }  // predicated loads
+  const uint32_t w0 = __ldg(q), w1 = __ldg(q + 1), w2 = __ldg(q + 2);
   const int sh = a << Pack<BITS>::kLogBits;
   lo = __funnelshift_r(w0, w1, sh);
   hi = __funnelshift_r(w1, w2, sh);
 }
 
 // Matching bases at the front of P[v..] and T[h..] within one 64-bit window (kWin if identical).
+// v and h must be positions inside the reads (the loads are unconditional).
 template <int BITS>
 __device__ __forceinline__ int match_window(const uint32_t* __restrict__ words, const SeqView& P,
-                                            const SeqView& T, int v, int h, bool on = true) {
+                                            const SeqView& T, int v, int h) {
   uint32_t pl, ph, tl, th;
-  window64<BITS>(words, P, v, on, pl, ph);
-  window64<BITS>(words, T, h, on, tl, th);
+  window64<BITS>(words, P, v, pl, ph);
+  window64<BITS>(words, T, h, tl, th);
   const uint32_t xl = pl ^ tl, xh = ph ^ th;
   const uint32_t sel = xl ? xl : xh;
-  const int bit = (__ffs(sel) - 1) + (xl ? 0 : 32);
-  return sel ? (bit >> Pack<BITS>::kLogBits) : Pack<BITS>::kWin;
+  // first differing bit; identical windows give ffs = 0 -> 0xffffffff, clamped to kWin
+  const uint32_t bit = (uint32_t)(__ffs(sel) - 1) | (xl ? 0u : 32u);
+  return (int)min(bit >> Pack<BITS>::kLogBits, (uint32_t)Pack<BITS>::kWin);
 }
 
 struct EditJob {
@@ -128,7 +162,8 @@ struct EditJob {
 template <int BITS>
 __device__ __forceinline__ int lcp_warp(const EditJob& J, int v, int h, int rem, const int lane) {
   constexpr int WIN = Pack<BITS>::kWin;
-  int m = match_window<BITS>(J.words, J.P, J.T, v, h, rem > 0);
+  const bool on = rem > 0;  // idle lanes probe position 0 of both reads and discard the result
+  int m = match_window<BITS>(J.words, J.P, J.T, on ? v : 0, on ? h : 0);
   int n = max(min(m, rem), 0);  // clamp at a sequence end (the reference stops on its sentinels)
   bool cont = (m >= WIN) && (rem > WIN);
   unsigned pend = __ballot_sync(kFull, cont);
@@ -174,6 +209,86 @@ __device__ __forceinline__ int lcp_warp(const EditJob& J, int v, int h, int rem,
   return n;
 }
 
+// LCP of P[v..) and T[h..) for ONE warp-uniform position, all lanes cooperating (32 windows per
+// round).  rem = min(plen - v, tlen - h).
+template <int BITS>
+__device__ __forceinline__ int lcp_uniform(const EditJob& J, int v, int h, int rem, const int lane) {
+  constexpr int WIN = Pack<BITS>::kWin;
+  int got = 0;
+  while (rem > 0) {
+    const int o = lane * WIN;
+    int mm = 0;
+    bool stop = true;
+    if (o < rem) {
+      mm = match_window<BITS>(J.words, J.P, J.T, v + o, h + o);
+      const int lim = rem - o;
+      if (mm >= lim) mm = lim;
+      else stop = mm < WIN;
+    }
+    const unsigned b = __ballot_sync(kFull, stop);
+    if (b) {
+      const int f = __ffs(b) - 1;
+      return got + f * WIN + __shfl_sync(kFull, mm, f);
+    }
+    got += 32 * WIN; v += 32 * WIN; h += 32 * WIN; rem -= 32 * WIN;
+  }
+  return got;
+}
+
+// Bases matched at the front of one 64-bit window whose LAST base is replaced by a sentinel
+// difference: the result is 0..kWin-1, and kWin-1 means "all kWin-1 compared bases match" (the
+// caller continues from there).  That makes the clamp a single min with the remaining length.
+// Loads are unconditional: v and h may be any position a wavefront offset can take, null-derived
+// garbage included (the batch buffers are padded for that).
+template <int BITS>
+__device__ __forceinline__ uint32_t first_diff(const EditJob& J, int v, int h) {
+  uint32_t pl, ph, tl, th;
+  window64<BITS>(J.words, J.P, v, pl, ph);
+  window64<BITS>(J.words, J.T, h, tl, th);
+  const uint32_t xl = pl ^ tl, xh = (ph ^ th) | 0x80000000u;
+  const uint32_t sel = xl ? xl : xh;
+  uint32_t bit = (uint32_t)(__ffs(sel) - 1);
+  if (!xl) bit |= 32u;
+  return bit >> Pack<BITS>::kLogBits;
+}
+
+// Slow path of a pass: some lane's first window matched completely.  n = bases matched so far
+// from (v,h), rem = the limit, c = this lane's run is still pending.  A few rounds of private
+// windows, then every run still pending is finished by the whole warp.  Returns the new n.
+template <int BITS>
+__device__ __forceinline__ int lcp_more(const EditJob& J, const int lane, int v, int h, int rem,
+                                        bool c, int n) {
+  constexpr int WE = Pack<BITS>::kWin - 1;
+  unsigned pend;
+  for (int it = 0;; ++it) {
+    if (c) {
+      const int left = rem - n;
+      const uint32_t fd = first_diff<BITS>(J, v + n, h + n);
+      n += (int)min(fd, (uint32_t)left);
+      c = fd == (uint32_t)WE && left > WE;
+    }
+    pend = __ballot_sync(kFull, c);
+    if (pend == 0) return n;
+    if (__popc(pend) <= 2 || it >= 2) break;
+  }
+  while (pend) {
+    const int src = __ffs(pend) - 1;
+    pend &= pend - 1;
+    const int nn = __shfl_sync(kFull, n, src);
+    const int got = lcp_uniform<BITS>(J, __shfl_sync(kFull, v, src) + nn, __shfl_sync(kFull, h, src) + nn,
+                                      __shfl_sync(kFull, rem, src) - nn, lane);
+    if (lane == src) n += got;
+  }
+  return n;
+}
+
+// (m & a) | (~m & b) in one LOP3 (the compiler otherwise re-derives a predicate + SEL per round)
+__device__ __forceinline__ int bitsel(int m, int a, int b) {
+  int d;
+  asm("lop3.b32 %0, %1, %2, %3, 0xCA;" : "=r"(d) : "r"(m), "r"(a), "r"(b));
+  return d;
+}
+
 // Warp-uniform state of one alignment (lo/hi) + per-lane partials of the last pass.
 struct WfState {
   int lo, hi;  // live diagonal range
@@ -181,74 +296,126 @@ struct WfState {
   bool fin;    // per-lane: ends-free termination met on a diagonal this lane owns
 };
 
-// One pass over the wavefront.
-//   COMPUTE: build wavefront s+1 over [lo-1,hi+1] from wavefront s in place and trim it
-//            (wavefront_compute_edit.c:70-97 + wavefront_compute.c:376-409);
-//   EXTEND : extend every live offset, gather the cut-off distance minimum and (ends-free) the
-//            termination flag (wavefront_extend.c:203-260,122-168; wavefront_heuristic.c:223-239).
-// Within a pass a ring slot is only ever touched by the lane that owns it, so no intra-pass
-// synchronisation is needed; passes are separated by __syncwarp().
+// A value the compiler cannot re-derive, so it stays in its register instead of being recomputed
+// (ISETP + SEL) in every round of the loop.
+__device__ __forceinline__ int opaque(int x) {
+  asm volatile("" : "+r"(x));
+  return x;
+}
+
+// One pass over the wavefront, 64 diagonals per round: lane L owns the adjacent diagonals
+// kb + 2L and kb + 2L + 1 (one 64-bit ring access, two independent extensions in flight).
+//   COMPUTE: build wavefront s+1 over [lo-1,hi+1] from wavefront s in place
+//            (wavefront_compute_edit.c:70-97); the caller trims afterwards (wf_trim);
+//   EXTEND : extend every live offset and gather the per-lane minimum of the cut-off distance
+//            (wavefront_extend.c:203-260; wavefront_heuristic.c:223-239) and, ends-free, the
+//            termination flag (wavefront_extend.c:122-168).
+// Ring invariant (kept by every writer): slots outside [lo,hi] hold nulls, so the pass needs no
+// range guards.  Within a pass a slot is only touched by its owning lane; passes are separated by
+// __syncwarp().  The ALU pipe limits this loop (profiles/), hence: one rotating shuffle per
+// neighbour with the round edges blended in by a LOP3, the sentinel window (first_diff), the
+// cut-off distance taken from the stored value (a null gives a huge distance by itself), the
+// slow-path test on the clamped counts alone, and no guards on the window loads.
+struct LaneConst {  // per-lane constants of the pass, made once per pair
+  int mk0, mk31;         // all-ones on lane 0 / lane 31
+  int from_lo, from_hi;  // source lanes of the two rotating shuffles
+  __device__ __forceinline__ explicit LaneConst(int lane)
+      : mk0(opaque(lane == 0 ? -1 : 0)), mk31(opaque(lane == 31 ? -1 : 0)),
+        from_lo(opaque((lane + 31) & 31)), from_hi(opaque((lane + 1) & 31)) {}
+};
+
 template <int BITS, bool WIDE, bool EF, bool COMPUTE, bool EXTEND>
 __device__ __forceinline__ void wf_pass(const Ring<WIDE>& R, const EditJob& J, const int lane,
-                                        WfState& S) {
-  const int plen = J.plen, tlen = J.tlen;
-  const int ak = tlen - plen;
-  const int lo = S.lo, hi = S.hi;
-  const unsigned span = (unsigned)(hi - lo);
-  const int clo = COMPUTE ? lo - 1 : lo, chi = COMPUTE ? hi + 1 : hi;
-  int kmin = 0x7fffffff, kmax = (int)0x80000000;  // per-lane trimmed limits
-  int carry = kNull;                              // old M[kc-1]
+                                        const LaneConst& C, WfState& S) {
+  constexpr int WE = Pack<BITS>::kWin - 1;
+  const int plen = J.plen, tlen = J.tlen, ak = tlen - plen;
+  const int clo = COMPUTE ? S.lo - 1 : S.lo, chi = COMPUTE ? S.hi + 1 : S.hi;
+  const int mk0 = C.mk0, mk31 = C.mk31, from_lo = C.from_lo, from_hi = C.from_hi;
+  int kb = clo & ~1;  // even: the lane's pair of slots is 8-byte aligned
+  int k0 = kb + 2 * lane;
   int dmin = kBigDist;
   bool fin = false;
-  int k = clo + lane;
-  int mid = R.ld(k);
-  if ((unsigned)(k - lo) > span) mid = kNull;
-#ifdef OTGPU_UNROLL2
-#pragma unroll 2
-#endif
-  for (int kc = clo; kc <= chi; kc += 32, k += 32) {
-    int m, nxt = R.ld(k + 32);  // this lane's slot in the next chunk (still old)
-    if ((unsigned)(k + 32 - lo) > span) nxt = kNull;
+  typename Ring<WIDE>::Tok tc = R.tok(k0);
+  int2 cur = R.ld2(tc);
+  int prevy = kENull;  // lane 31: M[kb-1] of the next round
+  for (; kb <= chi; kb += 64, k0 += 64) {
+    const typename Ring<WIDE>::Tok tn = R.tok(k0 + 64);
+    const int2 nxt = R.ld2(tn);  // this lane's slots in the next round (still old)
+    int m0, m1;
     if (COMPUTE) {
-      int left = __shfl_up_sync(kFull, mid, 1);
-      int right = __shfl_down_sync(kFull, mid, 1);
-      const int edge = __shfl_sync(kFull, nxt, 0);
-      const int last = __shfl_sync(kFull, mid, 31);
-      if (lane == 0) left = carry;
-      if (lane == 31) right = edge;
-      carry = last;
-      m = max(right, max(left, mid) + 1);
+      // left neighbour of slot 0: lane-1's slot 1; lane 0 takes lane 31's slot 1 of the last round
+      const int left0 = __shfl_sync(kFull, bitsel(mk31, prevy, cur.y), from_lo);
+      // right neighbour of slot 1: lane+1's slot 0; lane 31 takes lane 0's slot 0 of the next round
+      const int right1 = __shfl_sync(kFull, bitsel(mk0, nxt.x, cur.x), from_hi);
+      prevy = cur.y;
+      m0 = max(cur.y, max(left0, cur.x) + 1);
+      m1 = max(right1, max(cur.x, cur.y) + 1);
     } else {
-      m = mid;
+      m0 = cur.x;
+      m1 = cur.y;
     }
-    mid = nxt;
-    // in-bounds <=> m >= 0, v >= 0, and neither sequence overrun (lanes beyond chi see only
-    // nulls and fail the first test)
-    const int v = m - k;
-    const int rem = min(plen - v, tlen - m);
-    const bool ok = (m | v | rem) >= 0;
+    cur = nxt;
+    // in-bounds <=> offset >= 0, v >= 0 and neither sequence overrun
+    const int v0 = m0 - k0, v1 = m1 - k0 - 1;
+    const int pr0 = plen - v0, tr0 = tlen - m0, pr1 = plen - v1, tr1 = tlen - m1;
+    const int rem0 = min(pr0, tr0), rem1 = min(pr1, tr1);
+    const bool ok0 = (m0 | v0 | rem0) >= 0, ok1 = (m1 | v1 | rem1) >= 0;
     if (EXTEND) {
-      m += lcp_warp<BITS>(J, v, m, ok ? rem : 0, lane);
-      if (ok) {
-        dmin = min(dmin, plen + max(k, ak) - m);  // = max(plen - v', tlen - m')
-        if (EF) {
-          const int left_v = plen - (m - k), left_h = tlen - m;
-          fin |= (left_h <= 0 && left_v <= J.pe) || (left_v <= 0 && left_h <= J.te);
+      int n0 = (int)min(first_diff<BITS>(J, v0, m0), (uint32_t)rem0);
+      int n1 = (int)min(first_diff<BITS>(J, v1, m1), (uint32_t)rem1);
+      // a count of WE = every compared base matched and more remain: rare, and tested on the
+      // counts alone (lanes that are out of bounds may raise it spuriously; lcp_more re-checks)
+      if (__any_sync(kFull, (n0 == WE) | (n1 == WE))) {
+        const bool c0 = ok0 && n0 == WE && rem0 > WE, c1 = ok1 && n1 == WE && rem1 > WE;
+        if (__any_sync(kFull, c0 | c1)) {  // each lane finishes one pending run per call
+          const int n = lcp_more<BITS>(J, lane, c0 ? v0 : v1, c0 ? m0 : m1, c0 ? rem0 : rem1, c0 | c1,
+                                       c0 ? n0 : n1);
+          if (c0) n0 = n; else n1 = n;
+          if (__any_sync(kFull, c0 & c1)) n1 = lcp_more<BITS>(J, lane, v1, m1, rem1, c0 & c1, n1);
         }
       }
+      m0 += n0;
+      m1 += n1;
+      if (EF) {
+        fin |= ok0 && ((tr0 - n0 <= 0 && pr0 - n0 <= J.pe) || (pr0 - n0 <= 0 && tr0 - n0 <= J.te));
+        fin |= ok1 && ((tr1 - n1 <= 0 && pr1 - n1 <= J.pe) || (pr1 - n1 <= 0 && tr1 - n1 <= J.te));
+      }
     }
-    R.st(k, ok ? m : kNull);  // slots just beyond chi get nulls: never read (range-guarded)
-    if (COMPUTE && ok) {
-      kmin = min(kmin, k);
-      kmax = max(kmax, k);
+    const int s0 = ok0 ? m0 : kENull, s1 = ok1 ? m1 : kENull;  // out of bounds / beyond range: nulls
+    if (EXTEND) {
+      // cut-off distance max(plen - v', tlen - h') = plen + max(k, tlen - plen) - offset
+      dmin = min(dmin, plen + max(k0, ak) - s0);
+      dmin = min(dmin, plen + max(k0 + 1, ak) - s1);
     }
+    R.st2(tc, s0, s1);
+    tc = tn;
   }
-  __syncwarp();  // the next pass maps diagonals to lanes differently
-  if (COMPUTE) {
-    S.lo = __reduce_min_sync(kFull, kmin);
-    S.hi = __reduce_max_sync(kFull, kmax);
-  }
+  __syncwarp();  // the next pass (and the trim/cut-off probes) map diagonals to lanes differently
   if (EXTEND) { S.dmin = dmin; S.fin = fin; }
+}
+
+// Trim after a compute pass over [S.lo-1, S.hi+1] (wavefront_compute.c:376-409): the new limits
+// are the first and last diagonal holding an in-bounds offset, i.e. a non-null slot.  Normally
+// both are found by one 32-wide probe from each end.  Returns false if the wavefront is empty.
+template <bool WIDE>
+__device__ __forceinline__ bool wf_trim(const Ring<WIDE>& R, const int lane, WfState& S) {
+  const int clo = S.lo - 1, chi = S.hi + 1;
+  // (slots outside [clo,chi] hold nulls, so the first probes need no range test)
+  unsigned bl = __ballot_sync(kFull, R.ld(clo + lane) >= 0);
+  unsigned bh = __ballot_sync(kFull, R.ld(chi - lane) >= 0);
+  int lo = clo, hi = chi;
+  while (bl == 0) {
+    lo += 32;
+    if (lo > chi) return false;
+    bl = __ballot_sync(kFull, R.ld(lo + lane) >= 0 && lo + lane <= chi);
+  }
+  while (bh == 0) {  // a non-null slot exists, so this ends
+    hi -= 32;
+    bh = __ballot_sync(kFull, R.ld(hi - lane) >= 0 && hi - lane >= clo);
+  }
+  S.lo = lo + __ffs(bl) - 1;
+  S.hi = hi - (__ffs(bh) - 1);
+  return true;
 }
 
 // wf_compute_distance_end2end, wavefront_heuristic.c:111-119
@@ -258,7 +425,9 @@ __device__ __forceinline__ int wf_dist(int off, int k, int plen, int ak) {
 
 // WF-adaptive cut-off (wavefront_heuristic.c:285-328), run after every extend.
 // dmin = warp-wide minimum distance of the live wavefront.
-template <bool WIDE>
+// FILL: write nulls over the diagonals that were cut off, so that every ring slot outside
+// [lo,hi] is null (the invariant wf_pass relies on instead of range guards).
+template <bool WIDE, bool FILL = false>
 __device__ __forceinline__ void wf_cutoff(const Ring<WIDE>& R, const int plen, const int tlen,
                                           const int lane, int dmin, WfState& S) {
   const int lo = S.lo, hi = S.hi, ak = tlen - plen;
@@ -285,8 +454,98 @@ __device__ __forceinline__ void wf_cutoff(const Ring<WIDE>& R, const int plen, c
       if (b) { nhi = kc - (__ffs(b) - 1); break; }
     }
   }
+  if (FILL) {
+    for (int k = lo + lane; k < nlo; k += 32) R.st(k, kENull);
+    for (int k = hi - lane; k > nhi; k -= 32) R.st(k, kENull);
+    __syncwarp();
+  }
   S.lo = nlo;
   S.hi = nhi;
+}
+
+// Generic halves of the cut-off scan, for the rare step on which the 32-wide edge probes of
+// wf_edges do not settle it (wavefront_heuristic.c:269-283).
+template <bool WIDE>
+__device__ __noinline__ int wf_scan_lo(const Ring<WIDE>& R, int from, int top, int plen, int ak, int dmin,
+                                       int lane) {
+  for (int kc = from; kc < top; kc += 32) {
+    const int k = kc + lane;
+    const int d = wf_dist(R.ld(k), k, plen, ak);
+    const unsigned b = __ballot_sync(kFull, k < top && (d - dmin <= kMaxDist));
+    if (b) return kc + __ffs(b) - 1;
+  }
+  return top;
+}
+template <bool WIDE>
+__device__ __noinline__ int wf_scan_hi(const Ring<WIDE>& R, int from, int bot, int plen, int ak, int dmin,
+                                       int lane) {
+  for (int kc = from; kc > bot; kc -= 32) {
+    const int k = kc - lane;
+    const int d = wf_dist(R.ld(k), k, plen, ak);
+    const unsigned b = __ballot_sync(kFull, k > bot && (d - dmin <= kMaxDist));
+    if (b) return kc - (__ffs(b) - 1);
+  }
+  return bot;
+}
+
+// Everything between two passes, on one pair of 32-wide probes of the ring (the first and the
+// last 32 slots of the candidate range [clo,chi]):
+//   trim         first / last non-null slot                      (wavefront_compute.c:376-409)
+//   termination  end-to-end: cut-off distance 0; ends-free: flags (wavefront_extend.c:45-68,122-168)
+//   cut-off      WF-adaptive(10,50,1) on the trimmed wavefront    (wavefront_heuristic.c:285-328)
+// and nulls written over what the cut-off removed (ring invariant).  Returns 1 = alignment done,
+// -1 = wavefront empty, 0 = go on with [S.lo,S.hi].
+template <bool WIDE, bool EF>
+__device__ __forceinline__ int wf_edges(const Ring<WIDE>& R, const int plen, const int tlen,
+                                        const int lane, const int clo, const int chi, WfState& S) {
+  const int ak = tlen - plen;
+  const int kl = clo + lane, kh = chi - lane;
+  const int pl = R.ld(kl), ph = R.ld(kh);  // slots outside [clo,chi] hold nulls
+  const unsigned bl = __ballot_sync(kFull, pl >= 0), bh = __ballot_sync(kFull, ph >= 0);
+  int lo, hi;
+  if (bl != 0 && bh != 0) {
+    lo = clo + __ffs(bl) - 1;
+    hi = chi - (__ffs(bh) - 1);
+  } else {  // more than 32 nulls at an end (or nothing left)
+    S.lo = clo + 1;
+    S.hi = chi - 1;
+    if (!wf_trim<WIDE>(R, lane, S)) return -1;
+    lo = S.lo;
+    hi = S.hi;
+  }
+  const int dm = __reduce_min_sync(kFull, S.dmin);
+  if (EF ? __any_sync(kFull, S.fin) : (dm == 0)) return 1;
+  if (hi - lo + 1 >= kMinWfLen) {
+    const int dmin = min(max(plen, tlen), dm);  // :230-237
+    const int top = min(ak, hi);                // :269
+    int nlo = lo;
+    if (lo < top) {
+      const int d = plen + max(kl, ak) - pl;  // a null slot gives a distance in the millions
+      const unsigned b = __ballot_sync(kFull, kl >= lo && kl < top && d - dmin <= kMaxDist);
+      if (b) nlo = clo + __ffs(b) - 1;
+      else if (clo + 32 >= top) nlo = top;
+      else nlo = wf_scan_lo<WIDE>(R, clo + 32, top, plen, ak, dmin, lane);
+    }
+    const int bot = max(ak, nlo);  // :277 (uses the already reduced lo)
+    int nhi = hi;
+    if (hi > bot) {
+      const int d = plen + max(kh, ak) - ph;
+      const unsigned b = __ballot_sync(kFull, kh <= hi && kh > bot && d - dmin <= kMaxDist);
+      if (b) nhi = chi - (__ffs(b) - 1);
+      else if (chi - 32 <= bot) nhi = bot;
+      else nhi = wf_scan_hi<WIDE>(R, chi - 32, bot, plen, ak, dmin, lane);
+    }
+    if (kl >= lo && kl < nlo) R.st(kl, kENull);
+    if (kh <= hi && kh > nhi) R.st(kh, kENull);
+    for (int k = kl + 32; k < nlo; k += 32) R.st(k, kENull);
+    for (int k = kh - 32; k > nhi; k -= 32) R.st(k, kENull);
+    __syncwarp();
+    lo = nlo;
+    hi = nhi;
+  }
+  S.lo = lo;
+  S.hi = hi;
+  return 0;
 }
 
 // Exact prune, end-to-end only, width >= 1000 (wavefront_compute_edit.c:214-269).
@@ -312,6 +571,9 @@ __device__ __forceinline__ bool wf_prune(const Ring<WIDE>& R, const int plen, co
   if (nlo > min(hi, ak + w)) return false;
   int nhi = min(hi, ak + w);  // last k in (nlo,hi] with |k-ak| <= w, else nlo
   if (nhi <= nlo) nhi = nlo;
+  for (int k = lo + lane; k < nlo; k += 32) R.st(k, kENull);  // keep the ring invariant
+  for (int k = hi - lane; k > nhi; k -= 32) R.st(k, kENull);
+  __syncwarp();
   S.lo = nlo;
   S.hi = nhi;
   return true;
@@ -326,6 +588,9 @@ __device__ int wfa_edit_run(const Ring<WIDE>& R, const EditJob& J, const int lan
   WfState S;
   int s = 0;
 
+  // ring invariant: every slot outside the live range [lo,hi] holds a null
+  R.fill_null(lane);
+  __syncwarp();
   // ---- wavefront 0 (wavefront_align.c:113-135 / :190-237) ----
   if (!EF) {
     S.lo = S.hi = 0;
@@ -333,30 +598,32 @@ __device__ int wfa_edit_run(const Ring<WIDE>& R, const EditJob& J, const int lan
   } else {
     S.lo = -J.pb;
     S.hi = J.tb;
-    if (S.hi - S.lo + 40 > cap) return kScoreOverflow;
+    if (S.hi - S.lo + 136 > cap) return kScoreOverflow;
     for (int k = S.lo + lane; k <= S.hi; k += 32) R.st(k, k > 0 ? k : 0);
   }
   __syncwarp();
-  wf_pass<BITS, WIDE, EF, false, true>(R, J, lane, S);
+  const LaneConst C(lane);
+  wf_pass<BITS, WIDE, EF, false, true>(R, J, lane, C, S);
+  int clo = S.lo, chi = S.hi;  // candidate range the next wf_edges trims
 
   for (;;) {
-    // termination: ends-free per-diagonal flags (wavefront_extend.c:122-168); end-to-end is done
-    // iff the cut-off distance hit 0, i.e. offset tlen on diagonal tlen-plen (:45-68)
-    if (__any_sync(kFull, EF ? S.fin : (S.dmin == 0))) return s;
-    if (S.hi - S.lo + 1 >= kMinWfLen)
-      wf_cutoff<WIDE>(R, plen, tlen, lane, __reduce_min_sync(kFull, S.dmin), S);
+    const int st = wf_edges<WIDE, EF>(R, plen, tlen, lane, clo, chi, S);
+    if (st != 0) return st > 0 ? s : -1;  // done | empty wavefront -> WF_STATUS_UNFEASIBLE
     ++s;
-    // the pass touches slots [lo-1, hi+1+31]; they must not alias inside the ring
-    if (!WIDE && S.hi - S.lo + 40 > cap) return kScoreOverflow;
+    // the pass touches slots [lo-2, hi+1+127] and relies on nulls outside [lo,hi]: no aliasing
+    if (!WIDE && S.hi - S.lo + 136 > cap) return kScoreOverflow;
     if (WIDE && !EF && S.hi - S.lo + 3 >= kPruneLen) {
       // the exact prune sits between compute and extend: run them as separate passes
-      wf_pass<BITS, WIDE, EF, true, false>(R, J, lane, S);
-      if (S.lo > S.hi) return -1;
+      wf_pass<BITS, WIDE, EF, true, false>(R, J, lane, C, S);
+      if (!wf_trim<WIDE>(R, lane, S)) return -1;
       if (!wf_prune<WIDE>(R, plen, tlen, lane, S)) return -1;
-      wf_pass<BITS, WIDE, EF, false, true>(R, J, lane, S);
+      wf_pass<BITS, WIDE, EF, false, true>(R, J, lane, C, S);
+      clo = S.lo;
+      chi = S.hi;
     } else {
-      wf_pass<BITS, WIDE, EF, true, true>(R, J, lane, S);
-      if (S.lo > S.hi) return -1;  // empty wavefront -> WF_STATUS_UNFEASIBLE
+      wf_pass<BITS, WIDE, EF, true, true>(R, J, lane, C, S);
+      clo = S.lo - 1;
+      chi = S.hi + 1;
     }
   }
 }
