@@ -126,7 +126,14 @@ template <int BITS>
 __device__ __forceinline__ void window64(const uint32_t* __restrict__ words, const SeqView& s,
                                          int p, uint32_t& lo, uint32_t& hi) {
   const int a = (BITS == 2) ? p : s.sh0 + p;
+#ifdef OTGPU_MADHI
+  // word index = word0 + (a >> kLogBpw) as one multiply-high-add: FMA pipe instead of the ALU pipe
+  uint32_t wi;
+  asm("mad.hi.s32 %0, %1, %2, %3;" : "=r"(wi) : "r"(a), "r"(1 << (32 - Pack<BITS>::kLogBpw)), "r"(s.word0));
+  const uint32_t* q = words + wi;
+#else
   const uint32_t* q = words + (s.word0 + (uint32_t)(a >> Pack<BITS>::kLogBpw));
+#endif
   const uint32_t w0 = __ldg(q), w1 = __ldg(q + 1), w2 = __ldg(q + 2);
   const int sh = a << Pack<BITS>::kLogBits;
   lo = __funnelshift_r(w0, w1, sh);
@@ -338,6 +345,9 @@ __device__ __forceinline__ void wf_pass(const Ring<WIDE>& R, const EditJob& J, c
   typename Ring<WIDE>::Tok tc = R.tok(k0);
   int2 cur = R.ld2(tc);
   int prevy = kENull;  // lane 31: M[kb-1] of the next round
+#ifdef OTGPU_UNROLL2
+#pragma unroll 2
+#endif
   for (; kb <= chi; kb += 64, k0 += 64) {
     const typename Ring<WIDE>::Tok tn = R.tok(k0 + 64);
     const int2 nxt = R.ld2(tn);  // this lane's slots in the next round (still old)
