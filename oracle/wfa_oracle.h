@@ -54,6 +54,13 @@ int wfo_affine_cigar(const char* pattern, int plen, const char* text, int tlen, 
                      int pb, int pe, int tb, int te, int x, int o, int e, int* score_out,
                      char* cigar, int cap);
 
+/* Edit distance with full CIGAR (WFAlignerEdit(Alignment, MemoryMed), src/compare.cpp:95):
+ * same offsets, heuristic and prune as wfo_edit_score; predecessor ties mismatch > deletion >
+ * insertion; linear CIGAR unpack.  Returns the CIGAR length (may exceed cap) or -1;
+ * *score_out = the edit score getAlignmentScore() reports.  [wfa_oracle_edit_cigar.c] */
+int wfo_edit_cigar(const char* pattern, int plen, const char* text, int tlen, int endsfree, int pb,
+                   int pe, int tb, int te, int* score_out, char* cigar, int cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -52,8 +52,19 @@ def port():
             l.wfo_affine_cigar.argtypes = [c_char_p, c_int, c_char_p, c_int, c_int, c_int, c_int,
                                            c_int, c_int, c_int, c_int, c_int, C.POINTER(c_int),
                                            c_char_p, c_int]
+        l.wfo_edit_cigar.restype = c_int
+        l.wfo_edit_cigar.argtypes = [c_char_p, c_int, c_char_p, c_int, c_int, c_int, c_int, c_int,
+                                     c_int, C.POINTER(c_int), c_char_p, c_int]
         _port = l
     return _port
+
+
+def port_edit_cigar(p, t, ef=0, pb=0, pe=0, tb=0, te=0):
+    """(score, CIGAR) of the C port's edit-distance aligner with CIGAR."""
+    buf = C.create_string_buffer(len(p) + len(t) + 8)
+    sc = c_int()
+    n = port().wfo_edit_cigar(p, len(p), t, len(t), ef, pb, pe, tb, te, C.byref(sc), buf, len(buf))
+    return sc.value, buf.raw[:max(n, 0)].decode()
 
 
 def have_ref():
