@@ -136,6 +136,17 @@ int otgpu_affine_cigars(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
                         int gap_ext, int32_t* scores_out, char* cigars_out,
                         const uint64_t* cigar_off, int32_t* cigar_len_out);
 
+/* ---- edit-distance alignment with full CIGAR ----------------------------------------------- */
+/* What `otter compare` does per allele pair (src/compare.cpp:50-66,95: WFAlignerEdit(Alignment,
+ * MemoryMed), alignEnd2End + getAlignmentScore + getAlignmentCigar): same wavefronts, heuristic
+ * and exact prune as otgpu_edit_scores, plus the CIGAR (ties mismatch > deletion > insertion,
+ * wavefront_compute_edit.c:152-195; linear unpack, wavefront_backtrace_buffer.c:266-312).
+ * Arguments and outputs as otgpu_affine_cigars; scores_out[i] = the edit score. */
+int otgpu_edit_cigars(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                      const uint64_t* read_off, const uint32_t* read_len, uint32_t n_reads,
+                      const otgpu_pair* pairs, uint64_t n_pairs, int32_t* scores_out,
+                      char* cigars_out, const uint64_t* cigar_off, int32_t* cigar_len_out);
+
 #ifdef __cplusplus
 }
 #endif

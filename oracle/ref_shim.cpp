@@ -105,6 +105,36 @@ int ref_cigar(int which, int endsfree, const char* p, int plen, int pb, int pe, 
   return n;
 }
 
+#ifndef OTTER_B200_IN_TREE
+}  // extern "C"
+// src/compare.cpp:17-24 and :50 (defined there, not declared in a header)
+class DistCompare {
+ public:
+  int i;
+  int j;
+  double edit;
+  double ops;
+  DistCompare(int _i, int _j, double _e, double _o) : i(_i), j(_j), edit(_e), ops(_o) {}
+};
+void get_distances(wfa::WFAligner& aligner, std::vector<ANALLELE>& subjs,
+                   std::vector<ANALLELE>& querys, std::vector<DistCompare>& distances);
+extern "C" {
+// The reference's own get_distances (src/compare.cpp:50-66) with the aligner compare builds
+// (:95).  Reads [0,n_subj) are the subjects, the rest the queries; out = rows {i, j, edit, ops}.
+void ref_get_distances(const char* bases, const uint64_t* off, const uint32_t* len, uint32_t n_subj,
+                       uint32_t n_query, double* out) {
+  std::vector<ANALLELE> subjs, querys;
+  for (uint32_t i = 0; i < n_subj; ++i) subjs.emplace_back(std::string(bases + off[i], len[i]));
+  for (uint32_t i = n_subj; i < n_subj + n_query; ++i)
+    querys.emplace_back(std::string(bases + off[i], len[i]));
+  std::vector<DistCompare> d;
+  get_distances(tls().edit_cigar, subjs, querys, d);
+  for (size_t r = 0; r < d.size(); ++r) {
+    out[4 * r] = d[r].i; out[4 * r + 1] = d[r].j; out[4 * r + 2] = d[r].edit; out[4 * r + 3] = d[r].ops;
+  }
+}
+#endif
+
 // span bits: 1 = is_spanning_l, 2 = is_spanning_r.
 double ref_align_anreads(const char* x, uint32_t xlen, int xspan, const char* y, uint32_t ylen,
                          int yspan) {

@@ -14,6 +14,7 @@ SYMBOLS = [
     "otgpu_host_free", "otgpu_edit_scores", "otgpu_region_edit_scores",
     "otgpu_batch_upload_regions", "otgpu_batch_upload_pairs", "otgpu_batch_align",
     "otgpu_batch_download", "otgpu_synchronize", "otgpu_last_align_ms", "otgpu_affine_cigars",
+    "otgpu_edit_cigars",
 ]
 
 
@@ -72,6 +73,7 @@ def lib():
         l.otgpu_synchronize.argtypes = [vp]
         l.otgpu_last_align_ms.argtypes = [vp, C.POINTER(C.c_float * 4)]
         l.otgpu_affine_cigars.argtypes = [vp, vp, u64, vp, vp, u32, vp, u64, i32, i32, i32, vp, vp, vp, vp]
+        l.otgpu_edit_cigars.argtypes = [vp, vp, u64, vp, vp, u32, vp, u64, vp, vp, vp, vp]
         _lib = l
     return _lib
 
@@ -150,7 +152,11 @@ class Context:
                                                   _p(score_off), n_scores, _p(out)))
         return out
 
-    def affine_cigars(self, bases, off, lens, pairs, x=4, o=6, e=2):
+    def edit_cigars(self, bases, off, lens, pairs):
+        """Edit distance with CIGAR (compare's aligner) -> (scores, CIGAR bytes | status)."""
+        return self.affine_cigars(bases, off, lens, pairs, edit=True)
+
+    def affine_cigars(self, bases, off, lens, pairs, x=4, o=6, e=2, edit=False):
         """-> (scores int32[n], list of CIGAR bytes or negative status ints)."""
         pairs = np.ascontiguousarray(pairs, dtype=PAIR_DTYPE)
         n = len(pairs)
@@ -161,9 +167,14 @@ class Context:
         scores = np.zeros(n, dtype=np.int32)
         clen = np.zeros(n, dtype=np.int32)
         cig = np.zeros(int(coff[-1]) + 1, dtype=np.uint8)
-        self._ck(self._l.otgpu_affine_cigars(self._h, _p(bases), bases.size, _p(off), _p(lens),
-                                             len(lens), _p(pairs), n, x, o, e, _p(scores), _p(cig),
-                                             _p(coff), _p(clen)))
+        if edit:
+            self._ck(self._l.otgpu_edit_cigars(self._h, _p(bases), bases.size, _p(off), _p(lens),
+                                               len(lens), _p(pairs), n, _p(scores), _p(cig),
+                                               _p(coff), _p(clen)))
+        else:
+            self._ck(self._l.otgpu_affine_cigars(self._h, _p(bases), bases.size, _p(off), _p(lens),
+                                                 len(lens), _p(pairs), n, x, o, e, _p(scores),
+                                                 _p(cig), _p(coff), _p(clen)))
         out = []
         for i in range(n):
             out.append(cig[int(coff[i]):int(coff[i]) + int(clen[i])].tobytes() if clen[i] >= 0

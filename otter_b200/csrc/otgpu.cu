@@ -12,6 +12,7 @@
 #include "../../include/otter_b200.h"
 #include "wfa_edit.cuh"
 #include "wfa_affine.cuh"
+#include "wfa_edit_cigar.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -624,17 +625,17 @@ namespace {
 
 // Gap-affine + CIGAR: persistent warps, one pair per warp, per-warp HBM workspace.
 // RETRY = second pass over the pairs whose trace outgrew the first-tier slab.
-template <bool RETRY>
+template <bool RETRY, bool EDIT>
 __global__ void __launch_bounds__(kCtaThreads)
 k_affine(DevBatch b, Counters* __restrict__ ctr, uint32_t* __restrict__ ovf_list, AffPen pen,
          int32_t* __restrict__ rings, int wcap, uint8_t* __restrict__ slab, uint32_t slab_bytes,
          uint8_t* __restrict__ ops, uint32_t ops_cap, const uint64_t* __restrict__ cigar_off,
          char* __restrict__ cigars, int32_t* __restrict__ cigar_len) {
-  __shared__ AffSlot meta_smem[kWarpsPerCta][kAffMaxScope];
+  __shared__ AffSlot meta_smem[kWarpsPerCta][EDIT ? 1 : kAffMaxScope];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const size_t gw = (size_t)blockIdx.x * kWarpsPerCta + warp;
   AffWork W;
-  W.rings = rings + gw * 3 * (size_t)pen.scope * wcap;
+  W.rings = rings + gw * (EDIT ? 2 : 3 * (size_t)pen.scope) * wcap;
   W.wmask = wcap - 1;
   W.slab = slab + gw * (size_t)slab_bytes;
   W.slab_bytes = slab_bytes;
@@ -660,11 +661,13 @@ k_affine(DevBatch b, Counters* __restrict__ ctr, uint32_t* __restrict__ ovf_list
     if (bytes) {
       J.words = reinterpret_cast<const uint32_t*>(b.bases);
       J.P = view8(b, pr.pattern); J.T = view8(b, pr.text);
-      len = wfa_affine_pair<8>(W, meta_smem[warp], J, pen, lane, cigars + c0, cap, &score);
+      len = EDIT ? wfa_editcigar_pair<8>(W, J, lane, cigars + c0, cap, &score)
+                 : wfa_affine_pair<8>(W, meta_smem[warp], J, pen, lane, cigars + c0, cap, &score);
     } else {
       J.words = b.packed;
       J.P = view2(b, pr.pattern); J.T = view2(b, pr.text);
-      len = wfa_affine_pair<2>(W, meta_smem[warp], J, pen, lane, cigars + c0, cap, &score);
+      len = EDIT ? wfa_editcigar_pair<2>(W, J, lane, cigars + c0, cap, &score)
+                 : wfa_affine_pair<2>(W, meta_smem[warp], J, pen, lane, cigars + c0, cap, &score);
     }
     __syncwarp();
     if (lane == 0) {
@@ -682,18 +685,14 @@ k_affine(DevBatch b, Counters* __restrict__ ctr, uint32_t* __restrict__ ovf_list
 
 }  // namespace
 
-extern "C" int otgpu_affine_cigars(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
-                                   const uint64_t* read_off, const uint32_t* read_len,
-                                   uint32_t n_reads, const otgpu_pair* pairs, uint64_t n_pairs,
-                                   int mismatch, int gap_open, int gap_ext, int32_t* scores_out,
-                                   char* cigars_out, const uint64_t* cigar_off,
-                                   int32_t* cigar_len_out) {
+namespace {
+// Alignments with CIGAR, gap-affine (edit = false) or edit distance (edit = true): same batch
+// upload, per-warp HBM workspace, two-tier trace slab and result download.
+int cigars_impl(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const uint64_t* read_off,
+                const uint32_t* read_len, uint32_t n_reads, const otgpu_pair* pairs,
+                uint64_t n_pairs, const bool edit, AffPen pen, int32_t* scores_out, char* cigars_out,
+                const uint64_t* cigar_off, int32_t* cigar_len_out) {
   if (!ctx || ((!scores_out || !cigar_off || !cigar_len_out) && n_pairs)) return OTGPU_ERR_ARGS;
-  // wavefronts_penalties_set_affine (wavefront_penalties.c:86-119): X>0, O>=0, E>0
-  if (mismatch <= 0 || gap_open < 0 || gap_ext <= 0) return OTGPU_ERR_ARGS;
-  AffPen pen{mismatch, gap_open, gap_ext, 0};
-  pen.scope = (gap_open + gap_ext > mismatch ? gap_open + gap_ext : mismatch) + 1;
-  if (pen.scope > kAffMaxScope) return OTGPU_ERR_ARGS;
   int s = otgpu_batch_upload_pairs(ctx, bases, n_bases, read_off, read_len, n_reads, pairs, n_pairs);
   if (s != OTGPU_OK) return s;
   if (n_pairs == 0) return OTGPU_OK;
@@ -706,7 +705,7 @@ extern "C" int otgpu_affine_cigars(otgpu_ctx* ctx, const uint8_t* bases, uint64_
   // per-warp workspace: rings cover every diagonal of the longest pair, so they never alias
   const int wcap = next_pow2(2 * (int)ctx->max_len + 64);
   const uint32_t ops_cap = 4u * ctx->max_len + 64u;
-  const size_t ring_bytes = (size_t)3 * pen.scope * wcap * 4;
+  const size_t ring_bytes = (size_t)(edit ? 2 : 3 * pen.scope) * wcap * 4;
   const uint32_t slab1 = 2u << 20;
   int grid = ctx->n_sm * 1;
   while (grid > 8 && (size_t)grid * kWarpsPerCta * (ring_bytes + slab1 + ops_cap) > ((size_t)24 << 30)) grid /= 2;
@@ -734,7 +733,7 @@ extern "C" int otgpu_affine_cigars(otgpu_ctx* ctx, const uint8_t* bases, uint64_
   k_pack_reads<<<n_reads, 128, 0, st>>>(b, static_cast<uint32_t*>(ctx->packed.p));
   Counters* ctr = static_cast<Counters*>(ctx->counters.p);
   uint32_t* ovf = static_cast<uint32_t*>(ctx->ovf_list.p);
-  k_affine<false><<<grid, kCtaThreads, 0, st>>>(
+  (edit ? k_affine<false, true> : k_affine<false, false>)<<<grid, kCtaThreads, 0, st>>>(
       b, ctr, ovf, pen, static_cast<int32_t*>(ctx->aff_rings.p), wcap,
       static_cast<uint8_t*>(ctx->aff_slab.p), slab1, static_cast<uint8_t*>(ctx->aff_ops.p), ops_cap,
       static_cast<const uint64_t*>(ctx->cigar_off.p), static_cast<char*>(ctx->cigars.p),
@@ -749,7 +748,7 @@ extern "C" int otgpu_affine_cigars(otgpu_ctx* ctx, const uint8_t* bases, uint64_
     int grid2 = (int)((n_retry + kWarpsPerCta - 1) / kWarpsPerCta);
     if (grid2 > 8) grid2 = 8;
     RS(aff_slab2, (size_t)grid2 * kWarpsPerCta * slab2);
-    k_affine<true><<<grid2, kCtaThreads, 0, st>>>(
+    (edit ? k_affine<true, true> : k_affine<true, false>)<<<grid2, kCtaThreads, 0, st>>>(
         b, ctr, ovf, pen, static_cast<int32_t*>(ctx->aff_rings.p), wcap,
         static_cast<uint8_t*>(ctx->aff_slab2.p), slab2, static_cast<uint8_t*>(ctx->aff_ops.p),
         ops_cap, static_cast<const uint64_t*>(ctx->cigar_off.p), static_cast<char*>(ctx->cigars.p),
@@ -764,4 +763,29 @@ extern "C" int otgpu_affine_cigars(otgpu_ctx* ctx, const uint8_t* bases, uint64_
   ctx->stats.n_pairs = n_pairs;
   ctx->stats.n_pairs_wide = n_retry;
   return OTGPU_OK;
+}
+}  // namespace
+
+extern "C" int otgpu_affine_cigars(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                                   const uint64_t* read_off, const uint32_t* read_len,
+                                   uint32_t n_reads, const otgpu_pair* pairs, uint64_t n_pairs,
+                                   int mismatch, int gap_open, int gap_ext, int32_t* scores_out,
+                                   char* cigars_out, const uint64_t* cigar_off,
+                                   int32_t* cigar_len_out) {
+  // wavefronts_penalties_set_affine (wavefront_penalties.c:86-119): X>0, O>=0, E>0
+  if (mismatch <= 0 || gap_open < 0 || gap_ext <= 0) return OTGPU_ERR_ARGS;
+  AffPen pen{mismatch, gap_open, gap_ext, 0};
+  pen.scope = (gap_open + gap_ext > mismatch ? gap_open + gap_ext : mismatch) + 1;
+  if (pen.scope > kAffMaxScope) return OTGPU_ERR_ARGS;
+  return cigars_impl(ctx, bases, n_bases, read_off, read_len, n_reads, pairs, n_pairs, false, pen,
+                     scores_out, cigars_out, cigar_off, cigar_len_out);
+}
+
+extern "C" int otgpu_edit_cigars(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                                 const uint64_t* read_off, const uint32_t* read_len,
+                                 uint32_t n_reads, const otgpu_pair* pairs, uint64_t n_pairs,
+                                 int32_t* scores_out, char* cigars_out, const uint64_t* cigar_off,
+                                 int32_t* cigar_len_out) {
+  return cigars_impl(ctx, bases, n_bases, read_off, read_len, n_reads, pairs, n_pairs, true,
+                     AffPen{1, 0, 1, 2}, scores_out, cigars_out, cigar_off, cigar_len_out);
 }

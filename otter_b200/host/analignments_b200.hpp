@@ -53,6 +53,12 @@ struct CigarJob {
 void affine_cigars(wfa::WFAligner& aligner2, const std::vector<CigarJob>& jobs,
                    std::vector<std::string>& cigars);
 
+// The same for either aligner flavour that produces CIGARs: gap-affine (aligner2) or edit
+// distance with CIGAR (`compare`'s WFAlignerEdit(Alignment), src/compare.cpp:95).
+// scores_out (optional) receives getAlignmentScore() per job.
+void batched_cigars(wfa::WFAligner& aligner, const std::vector<CigarJob>& jobs,
+                    std::vector<std::string>& cigars, std::vector<int>* scores_out);
+
 // local_realignment (src/analignments.cpp:11-60) with the two reference flanks already fetched
 // (ref_left = ref[start-flank,start), ref_right = ref[end,end+flank), upper-cased as
 // FaidxInstance::fetch does).  Mutates read.seq / spanning flags exactly like the reference.

@@ -6,6 +6,7 @@
 #include <memory>
 
 #include "analignments_b200.hpp"
+#include "compare_b200.hpp"
 
 namespace {
 std::vector<ANREAD> build_reads(const char* bases, const uint64_t* off, const uint32_t* len,
@@ -117,5 +118,35 @@ uint64_t othost_local_realignment(int flank, double min_sim, const char* ref_lef
     used += reads[i].seq.size();
   }
   return used;
+}
+
+// `compare`'s aligner facade (WFAlignerEdit(Alignment, MemoryMed), src/compare.cpp:95), one pair.
+int othost_edit_cigar(const char* p, int plen, const char* t, int tlen, int endsfree, int pb, int pe,
+                      int tb, int te, int* score, int* status, char* cigar, int cap) {
+  static thread_local std::unique_ptr<wfa::WFAlignerEdit> a;
+  if (!a) a.reset(new wfa::WFAlignerEdit(wfa::WFAligner::Alignment, wfa::WFAligner::MemoryMed));
+  const int st = endsfree ? a->alignEndsFree(p, plen, pb, pe, t, tlen, tb, te)
+                          : a->alignEnd2End(p, plen, t, tlen);
+  if (status) *status = st;
+  if (score) *score = a->getAlignmentScore();
+  const std::string c = a->getAlignmentCigar();
+  if (cigar && cap > 0) std::memcpy(cigar, c.data(), (int)c.size() < cap ? c.size() : cap);
+  return (int)c.size();
+}
+
+// get_distances (src/compare.cpp:50-66): reads [0,n_subj) are the subjects, the rest the queries.
+// out = n_subj * n_query rows of {i, j, edit, ops} as doubles, subject-major.
+void othost_get_distances(const char* bases, const uint64_t* off, const uint32_t* len,
+                          uint32_t n_subj, uint32_t n_query, double* out) {
+  static thread_local std::unique_ptr<wfa::WFAlignerEdit> a;
+  if (!a) a.reset(new wfa::WFAlignerEdit(wfa::WFAligner::Alignment, wfa::WFAligner::MemoryMed));
+  std::vector<ANALLELE> subjs, querys;
+  for (uint32_t i = 0; i < n_subj; ++i) subjs.emplace_back(std::string(bases + off[i], len[i]));
+  for (uint32_t i = n_subj; i < n_subj + n_query; ++i) querys.emplace_back(std::string(bases + off[i], len[i]));
+  std::vector<DistCompare> d;
+  get_distances(*a, subjs, querys, d);
+  for (size_t r = 0; r < d.size(); ++r) {
+    out[4 * r] = d[r].i; out[4 * r + 1] = d[r].j; out[4 * r + 2] = d[r].edit; out[4 * r + 3] = d[r].ops;
+  }
 }
 }

@@ -49,6 +49,17 @@ class ANREAD : public ANSEQ {
   void set_is_spanning() { is_spanning_l = is_spanning_r = true; }
 };
 
+// An assembled allele (reference src/anseqs.hpp:40-54); only the fields the hot path reads.
+class ANALLELE : public ANSEQ {
+ public:
+  int scov = 0, acov = 0, tcov = 0;
+  float se = 0.f;
+  int ic = 0;
+  HAPLOTAG hpt;
+  ANALLELE() {}
+  explicit ANALLELE(const std::string& s) : ANSEQ(s) {}
+};
+
 // Condensed upper-triangular distance store, row-major (0,1),(0,2)..(n-2,n-1): the layout
 // hclust-cpp consumes (reference include/hclust-cpp/fastcluster.h:45-51).
 class DistMatrix {

@@ -25,7 +25,14 @@ namespace {
 // -------------------------------------------------------------------------------------------------
 void affine_cigars(wfa::WFAligner& aligner2, const std::vector<CigarJob>& jobs,
                    std::vector<std::string>& cigars) {
+  batched_cigars(aligner2, jobs, cigars, nullptr);
+}
+
+// Gap-affine aligner -> otgpu_affine_cigars; edit aligner (compare's) -> otgpu_edit_cigars.
+void batched_cigars(wfa::WFAligner& aligner2, const std::vector<CigarJob>& jobs,
+                    std::vector<std::string>& cigars, std::vector<int>* scores_out) {
   cigars.assign(jobs.size(), std::string());
+  if (scores_out) scores_out->assign(jobs.size(), 0);
   if (jobs.empty()) return;
   otgpu_ctx* ctx = aligner2.context();
   if (!ctx) die("affine_cigars", OTGPU_ERR_NO_DEVICE, nullptr);
@@ -66,14 +73,20 @@ void affine_cigars(wfa::WFAligner& aligner2, const std::vector<CigarJob>& jobs,
   }
   std::vector<int32_t> scores(jobs.size()), clen(jobs.size());
   std::vector<char> cig(coff.back() + 1);
-  st = otgpu_affine_cigars(ctx, bases, used, off.data(), len.data(), (uint32_t)order.size(),
-                           pairs.data(), pairs.size(), aligner2.mismatch(), aligner2.gapOpening(),
-                           aligner2.gapExtension(), scores.data(), cig.data(), coff.data(),
-                           clen.data());
+  st = aligner2.isEdit()
+      ? otgpu_edit_cigars(ctx, bases, used, off.data(), len.data(), (uint32_t)order.size(),
+                          pairs.data(), pairs.size(), scores.data(), cig.data(), coff.data(),
+                          clen.data())
+      : otgpu_affine_cigars(ctx, bases, used, off.data(), len.data(), (uint32_t)order.size(),
+                            pairs.data(), pairs.size(), aligner2.mismatch(), aligner2.gapOpening(),
+                            aligner2.gapExtension(), scores.data(), cig.data(), coff.data(),
+                            clen.data());
   otgpu_host_free(pinned);
-  if (st != OTGPU_OK) die("affine_cigars", st, ctx);
-  for (size_t i = 0; i < jobs.size(); ++i)
+  if (st != OTGPU_OK) die("batched_cigars", st, ctx);
+  for (size_t i = 0; i < jobs.size(); ++i) {
     if (clen[i] >= 0) cigars[i].assign(cig.data() + coff[i], (size_t)clen[i]);
+    if (scores_out) (*scores_out)[i] = scores[i];
+  }
   // clen < 0 (unfeasible / OOM): the reference ignores the status and reads whatever CIGAR the
   // aligner holds; an empty string is the closest defined behaviour and is not reachable for the
   // end-to-end / ends-free forms otter issues.

@@ -26,7 +26,7 @@ class WFAligner {
     StatusMaxScoreReached = -2,   // WF_STATUS_MAX_SCORE_REACHED
     StatusOOM = -3,               // WF_STATUS_OOM
     StatusDeviceError = -100,     // CUDA failure (no reference equivalent; there is no fallback)
-    StatusNotOnDevice = -101      // this aligner flavour has no device kernel yet
+    StatusNotOnDevice = -101      // reserved: an aligner flavour without a device kernel (none now)
   };
   AlignmentStatus alignEnd2End(const char* pattern, int patternLength, const char* text,
                                int textLength);

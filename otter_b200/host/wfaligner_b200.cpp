@@ -26,12 +26,6 @@ WFAligner::AlignmentStatus WFAligner::run(const char* p, int plen, const char* t
                                           bool endsfree, int pb, int pe, int tb, int te) {
   cigar_.clear();
   if (!ctx_) { status_ = StatusDeviceError; return StatusDeviceError; }
-  if (kind_ == kEdit && scope_ != Score) {
-    // edit distance WITH CIGAR (only the `compare` command uses it, reference src/compare.cpp:95):
-    // SURVEY.md §8f row N1, no device kernel yet and no fallback
-    status_ = StatusNotOnDevice;
-    return StatusNotOnDevice;
-  }
   std::vector<uint8_t> bases((size_t)plen + (size_t)tlen + 1);
   std::memcpy(bases.data(), p, plen);
   std::memcpy(bases.data() + plen, t, tlen);
@@ -39,12 +33,17 @@ WFAligner::AlignmentStatus WFAligner::run(const char* p, int plen, const char* t
   const uint32_t len[2] = {(uint32_t)plen, (uint32_t)tlen};
   otgpu_pair pr{0, 1, endsfree ? pb : -1, pe, tb, te};
   int32_t sc = 0;
-  if (kind_ == kGapAffine) {  // score + CIGAR in one launch (wfa_affine.cuh)
+  if (kind_ == kGapAffine || scope_ == Alignment) {
+    // score + CIGAR in one launch: gap-affine (wfa_affine.cuh) or, for the aligner `compare`
+    // builds (reference src/compare.cpp:95), edit distance with CIGAR (wfa_edit_cigar.cuh)
     std::vector<char> cig((size_t)plen + tlen + 1);
     const uint64_t coff[2] = {0, (uint64_t)plen + tlen};
     int32_t clen = 0;
-    const int st = otgpu_affine_cigars(ctx_, bases.data(), (uint64_t)plen + tlen, off, len, 2, &pr, 1,
-                                       x_, o_, e_, &sc, cig.data(), coff, &clen);
+    const int st = kind_ == kGapAffine
+        ? otgpu_affine_cigars(ctx_, bases.data(), (uint64_t)plen + tlen, off, len, 2, &pr, 1, x_, o_,
+                              e_, &sc, cig.data(), coff, &clen)
+        : otgpu_edit_cigars(ctx_, bases.data(), (uint64_t)plen + tlen, off, len, 2, &pr, 1, &sc,
+                            cig.data(), coff, &clen);
     if (st != OTGPU_OK) { status_ = StatusDeviceError; return StatusDeviceError; }
     if (clen == OTGPU_SCORE_UNFEASIBLE) { status_ = StatusUnfeasible; return StatusUnfeasible; }
     if (clen < 0) { status_ = StatusOOM; return StatusOOM; }

@@ -51,6 +51,23 @@ def main():
                   ("AAAA", "TTTT"), ("ACGTACGTACGT", "ACGTTTTTACGTACGT"), ("N", "ACGT"),
                   ("NDNNN", "ACGTAC"), ("acgtACGT", "ACGTACGT")):
         add(a.encode(), b_.encode(), (0, 0, 0, 0, 0))
+    # whole get_distances calls (src/compare.cpp:50-66): subjects x queries -> {i, j, edit, ops}
+    out["get_distances"] = []
+    R.ref_get_distances.restype = None
+    R.ref_get_distances.argtypes = [C.c_void_p] * 3 + [C.c_uint32, C.c_uint32, C.c_void_p]
+    for tl, e in [(200, 0.02), (900, 0.05), (2500, 0.01)]:
+        reads = [S.b(r).decode() for r in S.tr_region(rng, 6, tl, e, extra_frac=0.3, n_rate=0.0)]
+        subj = [reads[0], reads[1]]
+        query = [reads[2], reads[3], reads[0], "N", "NDNNN", reads[4][: len(reads[0])]]
+        if tl == 900:
+            subj[1] = "N"
+        if tl == 2500:
+            subj[0] = "NDNNN"
+        seqs = [np.frombuffer(x.encode(), dtype=np.uint8) for x in subj + query]
+        bases, off, lens = S.pack_reads(seqs)
+        rows = np.zeros((len(subj) * len(query), 4), dtype=np.float64)
+        R.ref_get_distances(S.ptr(bases), S.ptr(off), S.ptr(lens), len(subj), len(query), S.ptr(rows))
+        out["get_distances"].append(dict(subjs=subj, querys=query, rows=rows.tolist()))
     path = os.path.join(HERE, "editcigar_golden.json")
     with open(path, "w") as f:
         json.dump(out, f)

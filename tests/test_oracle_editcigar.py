@@ -66,3 +66,25 @@ def test_port_equals_reference_random_edit_cigar():
             assert S.port_edit_cigar(x, y, *f) == (sc.value, buf.raw[:m].decode())
             n += 1
     assert n == 120
+
+
+def py_get_distances(subjs, querys):
+    """get_distances (src/compare.cpp:50-66) on top of the port's aligner: the host rules in Python."""
+    rows = []
+    for i, s in enumerate(subjs):
+        for j, q in enumerate(querys):
+            if s == q or (s == "N" and q == "NDNNN") or (q == "N" and s == "NDNNN"):
+                rows.append([i, j, 0, len(q)])
+            elif "N" in (s, q) or "NDNNN" in (s, q):
+                rows.append([i, j, len(q) - 1, len(q)])
+            else:
+                p, t = (s, q) if len(s) > len(q) else (q, s)
+                sc, cg = S.port_edit_cigar(p.encode(), t.encode())
+                rows.append([i, j, sc, len(cg)])
+    return rows
+
+
+def test_get_distances_rules_match_golden(egold):
+    assert len(egold["get_distances"]) == 3
+    for g in egold["get_distances"]:
+        assert py_get_distances(g["subjs"], g["querys"]) == [[int(x) for x in r] for r in g["rows"]]
