@@ -9,7 +9,7 @@ alignment (WFA, WF-adaptive heuristic, bit-exact to the reference) for the named
             kernels), CUDA events on the library's stream, max over ranks.
   e2e       pairs/s through the C-ABI call a host would make (otgpu_region_edit_scores) with
             PINNED HOST buffers: H2D of reads + kernels + D2H of scores inside the timed region.
-  roofline  dominant kernel k_align<false>: algorithmic bytes (2-bit reads once per pair + 4 B
+  roofline  dominant kernel k_align<1024> (k_align<2048> for long-read batches): algorithmic bytes (2-bit reads once per pair + 4 B
             score) / its CUDA-event duration, against MEASURED_PEAKS.json hbm_gbs.
   cpu_baseline  the reference's own fill_dist_matrix (oracle/_ref) — or our C port when the
             reference library is absent — on all host threads, on a bounded sample of the workload.
@@ -409,7 +409,7 @@ def main():
                     "d2h_bytes_per_step": int(n_pairs * 4), "ms_per_step": e2e_ms / args.steps,
                     "gcups_equiv": tot_cells * args.steps / (e2e_ms * 1e-3) / 1e9},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k_align<false>", "achieved": achieved,
+            "roofline": {"bound": "hbm", "kernel": "k_align<2048>" if B["lens"].max() > 8000 else "k_align<1024>", "achieved": achieved,
                          "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None,
                          "alg_bytes_per_launch": B["alg_bytes"], "kernel_ms": k_ms,

@@ -5,8 +5,8 @@
 //   -> k_pack_reads      raw bytes -> 2-bit words, flags reads holding a non-ACGT byte
 //   -> k_expand_regions  region table -> explicit (pattern,text) list in DistMatrix order,
 //                        pattern = longer read (reference src/analignments.cpp:67-70)
-//   -> k_align<false>    persistent warps, one pair per warp, wavefront ring in shared memory
-//   -> k_align<true>     the few pairs whose live width outgrew the ring, wavefront in HBM
+//   -> k_align<1024|2048> persistent warps, one pair per warp, wavefront ring in shared memory
+//   -> k_align<0>         the few pairs whose live width outgrew the ring, wavefront in HBM
 //   D2H(int32 scores)
 // There is no CPU path: every entry point needs a CUDA device.
 #include "../../include/otter_b200.h"
@@ -26,6 +26,7 @@ namespace {
 constexpr int kWarpsPerCta = 8;
 constexpr int kCtaThreads = kWarpsPerCta * 32;
 constexpr uint32_t kEmptySlot = 0xffffffffu;
+constexpr uint32_t kLongReadLen = 8000;  // batches with longer reads use the 2048-slot ring
 
 struct DevBatch {
   const uint8_t* bases;      // raw bytes, preceded and followed by kPadBases guard bytes
@@ -40,7 +41,7 @@ struct DevBatch {
   uint32_t n_reads;
 };
 
-// counters[0] main queue, [1] overflow count, [2] wide queue, [3] 8-bit pairs
+// counters[0] main queue, [1] wide (overflow) count, [2] wide queue, [3] 8-bit pairs
 struct Counters { unsigned long long v[4]; };
 
 __global__ void __launch_bounds__(128) k_pack_reads(DevBatch b, uint32_t* __restrict__ packed) {
@@ -147,29 +148,37 @@ __device__ __forceinline__ SeqView view8(const DevBatch& b, uint32_t r) {
 #ifndef OTGPU_ALIGN_MIN_CTAS
 #define OTGPU_ALIGN_MIN_CTAS 4
 #endif
-template <bool WIDE>
-__global__ void __launch_bounds__(kCtaThreads, OTGPU_ALIGN_MIN_CTAS)
-k_align(DevBatch b, Counters* __restrict__ ctr, const uint32_t* __restrict__ order,
-        uint32_t* __restrict__ ovf_list, int32_t* __restrict__ wide_ws, int wide_cap) {
+// One pair per warp.  CAP > 0: pairs named by `list` (count in ctr->v[count_slot], or all
+// b.n_pairs of them when count_slot < 0), wavefront ring of CAP slots in shared memory; pairs that
+// outgrow it go to ovf_list.  CAP == 0 ("wide"): the pairs of ovf_list, ring in HBM.
+// CAP = 1024 keeps 4 CTAs (32 warps) per SM; 2048 (3 CTAs) is for batches of long reads, whose
+// wavefronts pass a thousand diagonals.
+constexpr size_t ring_bytes(int cap) { return (size_t)(kWarpsPerCta + 1) * cap * 4; }
+template <int CAP>
+__global__ void __launch_bounds__(kCtaThreads, CAP == 2048 ? 3 : OTGPU_ALIGN_MIN_CTAS)
+k_align(DevBatch b, Counters* __restrict__ ctr, const uint32_t* __restrict__ list, int count_slot,
+        int cursor_slot, uint32_t* __restrict__ ovf_list, int32_t* __restrict__ wide_ws,
+        int wide_cap) {
   // one extra ring of slack: the rings are aligned to their size at run time (Ring<false>::addr
   // ORs the slot offset into the base), whatever offset the static allocation starts at
-  __shared__ int32_t ring_smem[WIDE ? 1 : (kWarpsPerCta + 1) * kRingCap];
+  constexpr bool WIDE = CAP == 0;
+  extern __shared__ int32_t ring_smem[];  // ring_bytes(CAP) of dynamic shared memory
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  Ring<WIDE> ring;
+  Ring<CAP> ring;
   if constexpr (WIDE) {
     ring.p = wide_ws + (size_t)(blockIdx.x * kWarpsPerCta + warp) * wide_cap;
     ring.mask = wide_cap - 1;
   } else {
-    const unsigned a0 = ((unsigned)__cvta_generic_to_shared(ring_smem) + kRingCap * 4 - 1) & ~(kRingCap * 4 - 1u);
-    ring.base = a0 + warp * (kRingCap * 4);
+    const unsigned a0 = ((unsigned)__cvta_generic_to_shared(ring_smem) + CAP * 4 - 1) & ~(CAP * 4 - 1u);
+    ring.base = a0 + warp * (CAP * 4);
   }
-  const unsigned long long limit = WIDE ? ctr->v[1] : b.n_pairs;
+  const unsigned long long limit = WIDE ? ctr->v[1] : (count_slot < 0 ? b.n_pairs : ctr->v[count_slot]);
   for (;;) {
     unsigned long long q = 0;
-    if (lane == 0) q = atomicAdd(&ctr->v[WIDE ? 2 : 0], 1ull);
+    if (lane == 0) q = atomicAdd(&ctr->v[WIDE ? 2 : cursor_slot], 1ull);
     q = __shfl_sync(kFull, q, 0);
     if (q >= limit) break;
-    const uint64_t idx = WIDE ? ovf_list[q] : order[q];
+    const uint64_t idx = WIDE ? ovf_list[q] : list[q];
     const otgpu_pair pr = b.pairs[idx];
     if (pr.pattern == kEmptySlot) {
       if (lane == 0) b.scores[idx] = 0;
@@ -185,12 +194,12 @@ k_align(DevBatch b, Counters* __restrict__ ctr, const uint32_t* __restrict__ ord
     if (bytes) {
       J.words = reinterpret_cast<const uint32_t*>(b.bases);
       J.P = view8(b, pr.pattern); J.T = view8(b, pr.text);
-      score = wfa_edit_pair<8, WIDE>(ring, J, lane);
+      score = wfa_edit_pair<8, CAP>(ring, J, lane);
       if (!WIDE && lane == 0) atomicAdd(&ctr->v[3], 1ull);
     } else {
       J.words = b.packed;
       J.P = view2(b, pr.pattern); J.T = view2(b, pr.text);
-      score = wfa_edit_pair<2, WIDE>(ring, J, lane);
+      score = wfa_edit_pair<2, CAP>(ring, J, lane);
     }
     __syncwarp();
     if (lane == 0) {
@@ -227,7 +236,8 @@ struct otgpu_ctx {
   bool resident = false, by_regions = false;
   uint64_t n_bases = 0, n_pairs = 0, n_packed_words = 0;
   uint32_t n_reads = 0, n_regions = 0, max_len = 0;
-  int grid_main = 0, grid_wide = 0, wide_cap = 0;
+  int grid_main = 0, grid_main_long = 0, grid_wide = 0, wide_cap = 0, wide_per_sm = 2;
+  int force_ring = 0;  // OTGPU_RING_SLOTS=1024|2048 at otgpu_create: pin the ring tier (tests)
   otgpu_stats stats = {0, 0, 0, 0};
   cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // pack|expand|align|wide|end
   bool timed = false;
@@ -329,13 +339,23 @@ int upload_reads(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const u
 int size_launch(otgpu_ctx* ctx) {
   if (ctx->grid_main == 0) {
     int per_sm = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_align<false>, kCtaThreads, 0));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_align<1024>, kCtaThreads, ring_bytes(1024)));
     if (per_sm < 1) per_sm = 1;
     ctx->grid_main = ctx->n_sm * per_sm;
+    CK(cudaFuncSetAttribute(k_align<2048>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            (int)ring_bytes(2048)));
+    cudaFuncSetAttribute(k_align<2048>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                         cudaSharedmemCarveoutMaxShared);
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_align<2048>, kCtaThreads, ring_bytes(2048)));
+    if (per_sm < 1) per_sm = 1;
+    ctx->grid_main_long = ctx->n_sm * per_sm;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_align<0>, kCtaThreads, 0));
+    if (per_sm < 1) per_sm = 1;
+    ctx->wide_per_sm = per_sm;
   }
   // wide fallback: ring must hold every diagonal of the longest possible pair
   const int need = next_pow2(2 * (int)ctx->max_len + 256);
-  int grid_wide = ctx->n_sm * 2;
+  int grid_wide = ctx->n_sm * ctx->wide_per_sm;  // full occupancy: the wide pairs are the heaviest
   const size_t budget = (size_t)4 << 30;
   while (grid_wide > 1 && (size_t)grid_wide * kWarpsPerCta * need * 4 > budget) grid_wide /= 2;
   ctx->wide_cap = need;
@@ -378,6 +398,10 @@ int otgpu_create(int device, otgpu_ctx** out) {
   otgpu_ctx* ctx = new (std::nothrow) otgpu_ctx();
   if (!ctx) return OTGPU_ERR_OOM;
   ctx->device = device;
+  if (const char* rs = getenv("OTGPU_RING_SLOTS")) {
+    const int v = atoi(rs);
+    if (v == 1024 || v == 2048) ctx->force_ring = v;
+  }
   cudaError_t e = cudaSetDevice(device);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&ctx->n_sm, cudaDevAttrMultiProcessorCount, device);
@@ -554,10 +578,14 @@ int otgpu_batch_align(otgpu_ctx* ctx) {
     Counters* ctr = static_cast<Counters*>(ctx->counters.p);
     uint32_t* ovf = static_cast<uint32_t*>(ctx->ovf_list.p);
     uint32_t* order = static_cast<uint32_t*>(ctx->order.p);
-    k_align<false><<<ctx->grid_main, kCtaThreads, 0, st>>>(b, ctr, order, ovf, nullptr, 0);
+    // wavefront width grows with read length: batches of long reads get the 2048-slot ring
+    if (ctx->force_ring ? ctx->force_ring == 2048 : ctx->max_len > kLongReadLen)
+      k_align<2048><<<ctx->grid_main_long, kCtaThreads, ring_bytes(2048), st>>>(b, ctr, order, -1, 0, ovf, nullptr, 0);
+    else
+      k_align<1024><<<ctx->grid_main, kCtaThreads, ring_bytes(1024), st>>>(b, ctr, order, -1, 0, ovf, nullptr, 0);
     CK(cudaEventRecord(ctx->ev[3], st));
-    k_align<true><<<ctx->grid_wide, kCtaThreads, 0, st>>>(
-        b, ctr, order, ovf, static_cast<int32_t*>(ctx->wide_ws.p), ctx->wide_cap);
+    k_align<0><<<ctx->grid_wide, kCtaThreads, 0, st>>>(
+        b, ctr, ovf, 1, 2, ovf, static_cast<int32_t*>(ctx->wide_ws.p), ctx->wide_cap);
     ctx->stats.kernel_launches += 2;
   } else {
     CK(cudaEventRecord(ctx->ev[3], st));

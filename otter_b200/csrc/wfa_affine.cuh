@@ -132,10 +132,10 @@ __device__ int wfa_affine_pair(const AffWork& W, AffSlot* __restrict__ meta, con
       }
       if (S.lo <= S.hi) {  // wavefront_heuristic.c:470-509
         if (S.hi - S.lo + 1 >= kMinWfLen) {
-          Ring<true> R;
+          Ring<0> R;
           R.p = m;
           R.mask = mask;
-          wf_cutoff<true>(R, plen, tlen, lane, __reduce_min_sync(kFull, dmin), S);
+          wf_cutoff<0>(R, plen, tlen, lane, __reduce_min_sync(kFull, dmin), S);
         }
         if (lane == 0) {
           AffSlot& a = meta[sm];

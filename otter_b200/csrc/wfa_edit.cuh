@@ -44,7 +44,6 @@ constexpr int kMaxDist = 50;    // wavefront_attributes.c:75
 constexpr int kPruneLen = 1000; // wavefront_compute_edit.c:224
 constexpr int kScoreOverflow = -2;  // internal: live width exceeded the shared-memory ring
 constexpr int kBigDist = 1 << 30;   // distance of a null offset, wavefront_heuristic.c:118
-constexpr int kRingCap = 1024;      // int32 slots per warp in shared memory (4 KiB, 4 KiB aligned)
 
 // ---- wavefront ring ---------------------------------------------------------------------------
 __device__ __forceinline__ int lds32(unsigned a) {
@@ -56,13 +55,13 @@ __device__ __forceinline__ void sts32(unsigned a, int v) {
   asm volatile("st.shared.s32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
 }
 
-template <bool WIDE>
-struct Ring;
-template <>
-struct Ring<false> {  // shared memory, fixed capacity, 32-bit shared-window addressing
+// Ring<CAP>: CAP int32 slots in shared memory (CAP a power of two), or, CAP == 0, an HBM
+// workspace whose capacity covers every diagonal of the pair ("wide").
+template <int CAP>
+struct Ring {         // shared memory, fixed capacity, 32-bit shared-window addressing
   unsigned base;      // aligned to the ring size, so slot address = base | ((k*4) & mask): one LOP3
-  static constexpr unsigned kMaskB = (kRingCap - 1) * 4;
-  __device__ __forceinline__ int cap() const { return kRingCap; }
+  static constexpr unsigned kMaskB = (CAP - 1) * 4;
+  __device__ __forceinline__ int cap() const { return CAP; }
   __device__ __forceinline__ unsigned addr(int k) const { return base | (((unsigned)k << 2) & kMaskB); }
   __device__ __forceinline__ int ld(int k) const { return lds32(addr(k)); }
   __device__ __forceinline__ void st(int k, int v) const { sts32(addr(k), v); }
@@ -80,13 +79,13 @@ struct Ring<false> {  // shared memory, fixed capacity, 32-bit shared-window add
   }
   __device__ __forceinline__ void fill_null(int lane) const {
 #pragma unroll
-    for (int i = 0; i < kRingCap / 128; ++i)
+    for (int i = 0; i < CAP / 128; ++i)
       asm volatile("st.shared.v4.s32 [%0], {%1, %1, %1, %1};" ::"r"(base + (i * 32 + lane) * 16), "r"(kENull)
                    : "memory");
   }
 };
 template <>
-struct Ring<true> {  // HBM workspace (L1/L2 cached), capacity covers every diagonal of the pair
+struct Ring<0> {  // HBM workspace (L1/L2 cached), capacity covers every diagonal of the pair
   int32_t* p;
   int mask;
   __device__ __forceinline__ int cap() const { return mask + 1; }
@@ -216,14 +215,30 @@ __device__ __forceinline__ int lcp_warp(const EditJob& J, int v, int h, int rem,
   return n;
 }
 
-// LCP of P[v..) and T[h..) for ONE warp-uniform position, all lanes cooperating (32 windows per
-// round).  rem = min(plen - v, tlen - h).
-template <int BITS>
-__device__ __forceinline__ int lcp_uniform(const EditJob& J, int v, int h, int rem, const int lane) {
+// A group of G lanes (the whole warp, or one of its halves) that works on one pair.  Every
+// warp-level primitive below takes the group: sync masks name only its lanes, lane indices are
+// relative to its first lane, so two half-warps can run two pairs through the same instruction
+// stream (k_align_dual) while the full-warp kernels compile to what they were.
+template <int G>
+struct Grp {
+  static constexpr int kLanes = G;
+  unsigned mask;  // lanes of the group
+  int gl;         // this lane's index inside the group
+  int first;      // warp lane of the group's lane 0
+  __device__ __forceinline__ explicit Grp(int lane)
+      : mask(G == 32 ? kFull : (0xffffu << (lane & 16))), gl(lane & (G - 1)), first(lane & ~(G - 1)) {}
+  // group-relative index of the first set bit of a ballot taken with `mask`
+  __device__ __forceinline__ int pos(unsigned ballot) const { return __ffs(ballot) - 1 - first; }
+};
+
+// LCP of P[v..) and T[h..) for ONE group-uniform position, all lanes of the group cooperating
+// (G windows per round).  rem = min(plen - v, tlen - h).
+template <int BITS, int G>
+__device__ __forceinline__ int lcp_uniform(const EditJob& J, int v, int h, int rem, const Grp<G>& g) {
   constexpr int WIN = Pack<BITS>::kWin;
   int got = 0;
   while (rem > 0) {
-    const int o = lane * WIN;
+    const int o = g.gl * WIN;
     int mm = 0;
     bool stop = true;
     if (o < rem) {
@@ -232,14 +247,18 @@ __device__ __forceinline__ int lcp_uniform(const EditJob& J, int v, int h, int r
       if (mm >= lim) mm = lim;
       else stop = mm < WIN;
     }
-    const unsigned b = __ballot_sync(kFull, stop);
+    const unsigned b = __ballot_sync(g.mask, stop);
     if (b) {
       const int f = __ffs(b) - 1;
-      return got + f * WIN + __shfl_sync(kFull, mm, f);
+      return got + (f - g.first) * WIN + __shfl_sync(g.mask, mm, f);
     }
-    got += 32 * WIN; v += 32 * WIN; h += 32 * WIN; rem -= 32 * WIN;
+    got += G * WIN; v += G * WIN; h += G * WIN; rem -= G * WIN;
   }
   return got;
+}
+template <int BITS>
+__device__ __forceinline__ int lcp_uniform(const EditJob& J, int v, int h, int rem, const int lane) {
+  return lcp_uniform<BITS, 32>(J, v, h, rem, Grp<32>(lane));
 }
 
 // Bases matched at the front of one 64-bit window whose LAST base is replaced by a sentinel
@@ -261,9 +280,9 @@ __device__ __forceinline__ uint32_t first_diff(const EditJob& J, int v, int h) {
 
 // Slow path of a pass: some lane's first window matched completely.  n = bases matched so far
 // from (v,h), rem = the limit, c = this lane's run is still pending.  A few rounds of private
-// windows, then every run still pending is finished by the whole warp.  Returns the new n.
-template <int BITS>
-__device__ __forceinline__ int lcp_more(const EditJob& J, const int lane, int v, int h, int rem,
+// windows, then every run still pending is finished by the whole group.  Returns the new n.
+template <int BITS, int G>
+__device__ __forceinline__ int lcp_more(const EditJob& J, const Grp<G>& g, int v, int h, int rem,
                                         bool c, int n) {
   constexpr int WE = Pack<BITS>::kWin - 1;
   unsigned pend;
@@ -274,17 +293,17 @@ __device__ __forceinline__ int lcp_more(const EditJob& J, const int lane, int v,
       n += (int)min(fd, (uint32_t)left);
       c = fd == (uint32_t)WE && left > WE;
     }
-    pend = __ballot_sync(kFull, c);
+    pend = __ballot_sync(g.mask, c);
     if (pend == 0) return n;
     if (__popc(pend) <= 2 || it >= 2) break;
   }
   while (pend) {
     const int src = __ffs(pend) - 1;
     pend &= pend - 1;
-    const int nn = __shfl_sync(kFull, n, src);
-    const int got = lcp_uniform<BITS>(J, __shfl_sync(kFull, v, src) + nn, __shfl_sync(kFull, h, src) + nn,
-                                      __shfl_sync(kFull, rem, src) - nn, lane);
-    if (lane == src) n += got;
+    const int nn = __shfl_sync(g.mask, n, src);
+    const int got = lcp_uniform<BITS, G>(J, __shfl_sync(g.mask, v, src) + nn, __shfl_sync(g.mask, h, src) + nn,
+                                         __shfl_sync(g.mask, rem, src) - nn, g);
+    if (g.gl + g.first == src) n += got;
   }
   return n;
 }
@@ -324,39 +343,41 @@ __device__ __forceinline__ int opaque(int x) {
 // cut-off distance taken from the stored value (a null gives a huge distance by itself), the
 // slow-path test on the clamped counts alone, and no guards on the window loads.
 struct LaneConst {  // per-lane constants of the pass, made once per pair
-  int mk0, mk31;         // all-ones on lane 0 / lane 31
-  int from_lo, from_hi;  // source lanes of the two rotating shuffles
-  __device__ __forceinline__ explicit LaneConst(int lane)
-      : mk0(opaque(lane == 0 ? -1 : 0)), mk31(opaque(lane == 31 ? -1 : 0)),
-        from_lo(opaque((lane + 31) & 31)), from_hi(opaque((lane + 1) & 31)) {}
+  int mk0, mk31;         // all-ones on the group's first / last lane
+  int from_lo, from_hi;  // source lanes (warp lane ids) of the two rotating shuffles
+  template <int G>
+  __device__ __forceinline__ explicit LaneConst(const Grp<G>& g)
+      : mk0(opaque(g.gl == 0 ? -1 : 0)), mk31(opaque(g.gl == G - 1 ? -1 : 0)),
+        from_lo(opaque(g.first | ((g.gl + G - 1) & (G - 1)))),
+        from_hi(opaque(g.first | ((g.gl + 1) & (G - 1)))) {}
 };
 
-template <int BITS, bool WIDE, bool EF, bool COMPUTE, bool EXTEND>
-__device__ __forceinline__ void wf_pass(const Ring<WIDE>& R, const EditJob& J, const int lane,
+template <int BITS, int CAP, bool EF, bool COMPUTE, bool EXTEND, int G>
+__device__ __forceinline__ void wf_pass(const Ring<CAP>& R, const EditJob& J, const Grp<G>& g,
                                         const LaneConst& C, WfState& S) {
   constexpr int WE = Pack<BITS>::kWin - 1;
   const int plen = J.plen, tlen = J.tlen, ak = tlen - plen;
   const int clo = COMPUTE ? S.lo - 1 : S.lo, chi = COMPUTE ? S.hi + 1 : S.hi;
   const int mk0 = C.mk0, mk31 = C.mk31, from_lo = C.from_lo, from_hi = C.from_hi;
   int kb = clo & ~1;  // even: the lane's pair of slots is 8-byte aligned
-  int k0 = kb + 2 * lane;
+  int k0 = kb + 2 * g.gl;
   int dmin = kBigDist;
   bool fin = false;
-  typename Ring<WIDE>::Tok tc = R.tok(k0);
+  typename Ring<CAP>::Tok tc = R.tok(k0);
   int2 cur = R.ld2(tc);
   int prevy = kENull;  // lane 31: M[kb-1] of the next round
 #ifdef OTGPU_UNROLL2
 #pragma unroll 2
 #endif
-  for (; kb <= chi; kb += 64, k0 += 64) {
-    const typename Ring<WIDE>::Tok tn = R.tok(k0 + 64);
+  for (; kb <= chi; kb += 2 * G, k0 += 2 * G) {
+    const typename Ring<CAP>::Tok tn = R.tok(k0 + 2 * G);
     const int2 nxt = R.ld2(tn);  // this lane's slots in the next round (still old)
     int m0, m1;
     if (COMPUTE) {
       // left neighbour of slot 0: lane-1's slot 1; lane 0 takes lane 31's slot 1 of the last round
-      const int left0 = __shfl_sync(kFull, bitsel(mk31, prevy, cur.y), from_lo);
+      const int left0 = __shfl_sync(g.mask, bitsel(mk31, prevy, cur.y), from_lo);
       // right neighbour of slot 1: lane+1's slot 0; lane 31 takes lane 0's slot 0 of the next round
-      const int right1 = __shfl_sync(kFull, bitsel(mk0, nxt.x, cur.x), from_hi);
+      const int right1 = __shfl_sync(g.mask, bitsel(mk0, nxt.x, cur.x), from_hi);
       prevy = cur.y;
       m0 = max(cur.y, max(left0, cur.x) + 1);
       m1 = max(right1, max(cur.x, cur.y) + 1);
@@ -375,13 +396,13 @@ __device__ __forceinline__ void wf_pass(const Ring<WIDE>& R, const EditJob& J, c
       int n1 = (int)min(first_diff<BITS>(J, v1, m1), (uint32_t)rem1);
       // a count of WE = every compared base matched and more remain: rare, and tested on the
       // counts alone (lanes that are out of bounds may raise it spuriously; lcp_more re-checks)
-      if (__any_sync(kFull, (n0 == WE) | (n1 == WE))) {
+      if (__any_sync(g.mask, (n0 == WE) | (n1 == WE))) {
         const bool c0 = ok0 && n0 == WE && rem0 > WE, c1 = ok1 && n1 == WE && rem1 > WE;
-        if (__any_sync(kFull, c0 | c1)) {  // each lane finishes one pending run per call
-          const int n = lcp_more<BITS>(J, lane, c0 ? v0 : v1, c0 ? m0 : m1, c0 ? rem0 : rem1, c0 | c1,
-                                       c0 ? n0 : n1);
+        if (__any_sync(g.mask, c0 | c1)) {  // each lane finishes one pending run per call
+          const int n = lcp_more<BITS, G>(J, g, c0 ? v0 : v1, c0 ? m0 : m1, c0 ? rem0 : rem1, c0 | c1,
+                                          c0 ? n0 : n1);
           if (c0) n0 = n; else n1 = n;
-          if (__any_sync(kFull, c0 & c1)) n1 = lcp_more<BITS>(J, lane, v1, m1, rem1, c0 & c1, n1);
+          if (__any_sync(g.mask, c0 & c1)) n1 = lcp_more<BITS, G>(J, g, v1, m1, rem1, c0 & c1, n1);
         }
       }
       m0 += n0;
@@ -400,31 +421,31 @@ __device__ __forceinline__ void wf_pass(const Ring<WIDE>& R, const EditJob& J, c
     R.st2(tc, s0, s1);
     tc = tn;
   }
-  __syncwarp();  // the next pass (and the trim/cut-off probes) map diagonals to lanes differently
+  __syncwarp(g.mask);  // the next pass (and the trim/cut-off probes) map diagonals to lanes differently
   if (EXTEND) { S.dmin = dmin; S.fin = fin; }
 }
 
 // Trim after a compute pass over [S.lo-1, S.hi+1] (wavefront_compute.c:376-409): the new limits
 // are the first and last diagonal holding an in-bounds offset, i.e. a non-null slot.  Normally
 // both are found by one 32-wide probe from each end.  Returns false if the wavefront is empty.
-template <bool WIDE>
-__device__ __forceinline__ bool wf_trim(const Ring<WIDE>& R, const int lane, WfState& S) {
+template <int CAP, int G>
+__device__ __forceinline__ bool wf_trim(const Ring<CAP>& R, const Grp<G>& g, WfState& S) {
   const int clo = S.lo - 1, chi = S.hi + 1;
   // (slots outside [clo,chi] hold nulls, so the first probes need no range test)
-  unsigned bl = __ballot_sync(kFull, R.ld(clo + lane) >= 0);
-  unsigned bh = __ballot_sync(kFull, R.ld(chi - lane) >= 0);
+  unsigned bl = __ballot_sync(g.mask, R.ld(clo + g.gl) >= 0);
+  unsigned bh = __ballot_sync(g.mask, R.ld(chi - g.gl) >= 0);
   int lo = clo, hi = chi;
   while (bl == 0) {
-    lo += 32;
+    lo += G;
     if (lo > chi) return false;
-    bl = __ballot_sync(kFull, R.ld(lo + lane) >= 0 && lo + lane <= chi);
+    bl = __ballot_sync(g.mask, R.ld(lo + g.gl) >= 0 && lo + g.gl <= chi);
   }
   while (bh == 0) {  // a non-null slot exists, so this ends
-    hi -= 32;
-    bh = __ballot_sync(kFull, R.ld(hi - lane) >= 0 && hi - lane >= clo);
+    hi -= G;
+    bh = __ballot_sync(g.mask, R.ld(hi - g.gl) >= 0 && hi - g.gl >= clo);
   }
-  S.lo = lo + __ffs(bl) - 1;
-  S.hi = hi - (__ffs(bh) - 1);
+  S.lo = lo + g.pos(bl);
+  S.hi = hi - g.pos(bh);
   return true;
 }
 
@@ -437,8 +458,8 @@ __device__ __forceinline__ int wf_dist(int off, int k, int plen, int ak) {
 // dmin = warp-wide minimum distance of the live wavefront.
 // FILL: write nulls over the diagonals that were cut off, so that every ring slot outside
 // [lo,hi] is null (the invariant wf_pass relies on instead of range guards).
-template <bool WIDE, bool FILL = false>
-__device__ __forceinline__ void wf_cutoff(const Ring<WIDE>& R, const int plen, const int tlen,
+template <int CAP, bool FILL = false>
+__device__ __forceinline__ void wf_cutoff(const Ring<CAP>& R, const int plen, const int tlen,
                                           const int lane, int dmin, WfState& S) {
   const int lo = S.lo, hi = S.hi, ak = tlen - plen;
   dmin = min(max(plen, tlen), dmin);  // :230-237
@@ -475,25 +496,25 @@ __device__ __forceinline__ void wf_cutoff(const Ring<WIDE>& R, const int plen, c
 
 // Generic halves of the cut-off scan, for the rare step on which the 32-wide edge probes of
 // wf_edges do not settle it (wavefront_heuristic.c:269-283).
-template <bool WIDE>
-__device__ __noinline__ int wf_scan_lo(const Ring<WIDE>& R, int from, int top, int plen, int ak, int dmin,
-                                       int lane) {
-  for (int kc = from; kc < top; kc += 32) {
-    const int k = kc + lane;
+template <int CAP, int G>
+__device__ __noinline__ int wf_scan_lo(const Ring<CAP>& R, int from, int top, int plen, int ak, int dmin,
+                                       const Grp<G>& g) {
+  for (int kc = from; kc < top; kc += G) {
+    const int k = kc + g.gl;
     const int d = wf_dist(R.ld(k), k, plen, ak);
-    const unsigned b = __ballot_sync(kFull, k < top && (d - dmin <= kMaxDist));
-    if (b) return kc + __ffs(b) - 1;
+    const unsigned b = __ballot_sync(g.mask, k < top && (d - dmin <= kMaxDist));
+    if (b) return kc + g.pos(b);
   }
   return top;
 }
-template <bool WIDE>
-__device__ __noinline__ int wf_scan_hi(const Ring<WIDE>& R, int from, int bot, int plen, int ak, int dmin,
-                                       int lane) {
-  for (int kc = from; kc > bot; kc -= 32) {
-    const int k = kc - lane;
+template <int CAP, int G>
+__device__ __noinline__ int wf_scan_hi(const Ring<CAP>& R, int from, int bot, int plen, int ak, int dmin,
+                                       const Grp<G>& g) {
+  for (int kc = from; kc > bot; kc -= G) {
+    const int k = kc - g.gl;
     const int d = wf_dist(R.ld(k), k, plen, ak);
-    const unsigned b = __ballot_sync(kFull, k > bot && (d - dmin <= kMaxDist));
-    if (b) return kc - (__ffs(b) - 1);
+    const unsigned b = __ballot_sync(g.mask, k > bot && (d - dmin <= kMaxDist));
+    if (b) return kc - g.pos(b);
   }
   return bot;
 }
@@ -505,51 +526,51 @@ __device__ __noinline__ int wf_scan_hi(const Ring<WIDE>& R, int from, int bot, i
 //   cut-off      WF-adaptive(10,50,1) on the trimmed wavefront    (wavefront_heuristic.c:285-328)
 // and nulls written over what the cut-off removed (ring invariant).  Returns 1 = alignment done,
 // -1 = wavefront empty, 0 = go on with [S.lo,S.hi].
-template <bool WIDE, bool EF>
-__device__ __forceinline__ int wf_edges(const Ring<WIDE>& R, const int plen, const int tlen,
-                                        const int lane, const int clo, const int chi, WfState& S) {
+template <int CAP, bool EF, int G>
+__device__ __forceinline__ int wf_edges(const Ring<CAP>& R, const int plen, const int tlen,
+                                        const Grp<G>& g, const int clo, const int chi, WfState& S) {
   const int ak = tlen - plen;
-  const int kl = clo + lane, kh = chi - lane;
+  const int kl = clo + g.gl, kh = chi - g.gl;
   const int pl = R.ld(kl), ph = R.ld(kh);  // slots outside [clo,chi] hold nulls
-  const unsigned bl = __ballot_sync(kFull, pl >= 0), bh = __ballot_sync(kFull, ph >= 0);
+  const unsigned bl = __ballot_sync(g.mask, pl >= 0), bh = __ballot_sync(g.mask, ph >= 0);
   int lo, hi;
   if (bl != 0 && bh != 0) {
-    lo = clo + __ffs(bl) - 1;
-    hi = chi - (__ffs(bh) - 1);
-  } else {  // more than 32 nulls at an end (or nothing left)
+    lo = clo + g.pos(bl);
+    hi = chi - g.pos(bh);
+  } else {  // more than G nulls at an end (or nothing left)
     S.lo = clo + 1;
     S.hi = chi - 1;
-    if (!wf_trim<WIDE>(R, lane, S)) return -1;
+    if (!wf_trim<CAP, G>(R, g, S)) return -1;
     lo = S.lo;
     hi = S.hi;
   }
-  const int dm = __reduce_min_sync(kFull, S.dmin);
-  if (EF ? __any_sync(kFull, S.fin) : (dm == 0)) return 1;
+  const int dm = __reduce_min_sync(g.mask, S.dmin);
+  if (EF ? __any_sync(g.mask, S.fin) : (dm == 0)) return 1;
   if (hi - lo + 1 >= kMinWfLen) {
     const int dmin = min(max(plen, tlen), dm);  // :230-237
     const int top = min(ak, hi);                // :269
     int nlo = lo;
     if (lo < top) {
       const int d = plen + max(kl, ak) - pl;  // a null slot gives a distance in the millions
-      const unsigned b = __ballot_sync(kFull, kl >= lo && kl < top && d - dmin <= kMaxDist);
-      if (b) nlo = clo + __ffs(b) - 1;
-      else if (clo + 32 >= top) nlo = top;
-      else nlo = wf_scan_lo<WIDE>(R, clo + 32, top, plen, ak, dmin, lane);
+      const unsigned b = __ballot_sync(g.mask, kl >= lo && kl < top && d - dmin <= kMaxDist);
+      if (b) nlo = clo + g.pos(b);
+      else if (clo + G >= top) nlo = top;
+      else nlo = wf_scan_lo<CAP, G>(R, clo + G, top, plen, ak, dmin, g);
     }
     const int bot = max(ak, nlo);  // :277 (uses the already reduced lo)
     int nhi = hi;
     if (hi > bot) {
       const int d = plen + max(kh, ak) - ph;
-      const unsigned b = __ballot_sync(kFull, kh <= hi && kh > bot && d - dmin <= kMaxDist);
-      if (b) nhi = chi - (__ffs(b) - 1);
-      else if (chi - 32 <= bot) nhi = bot;
-      else nhi = wf_scan_hi<WIDE>(R, chi - 32, bot, plen, ak, dmin, lane);
+      const unsigned b = __ballot_sync(g.mask, kh <= hi && kh > bot && d - dmin <= kMaxDist);
+      if (b) nhi = chi - g.pos(b);
+      else if (chi - G <= bot) nhi = bot;
+      else nhi = wf_scan_hi<CAP, G>(R, chi - G, bot, plen, ak, dmin, g);
     }
     if (kl >= lo && kl < nlo) R.st(kl, kENull);
     if (kh <= hi && kh > nhi) R.st(kh, kENull);
-    for (int k = kl + 32; k < nlo; k += 32) R.st(k, kENull);
-    for (int k = kh - 32; k > nhi; k -= 32) R.st(k, kENull);
-    __syncwarp();
+    for (int k = kl + G; k < nlo; k += G) R.st(k, kENull);
+    for (int k = kh - G; k > nhi; k -= G) R.st(k, kENull);
+    __syncwarp(g.mask);
     lo = nlo;
     hi = nhi;
   }
@@ -560,8 +581,8 @@ __device__ __forceinline__ int wf_edges(const Ring<WIDE>& R, const int plen, con
 
 // Exact prune, end-to-end only, width >= 1000 (wavefront_compute_edit.c:214-269).
 // Returns false if nothing survives (cannot happen: the minimum is attained inside [lo,hi]).
-template <bool WIDE>
-__device__ __forceinline__ bool wf_prune(const Ring<WIDE>& R, const int plen, const int tlen,
+template <int CAP>
+__device__ __forceinline__ bool wf_prune(const Ring<CAP>& R, const int plen, const int tlen,
                                          const int lane, WfState& S) {
   const int lo = S.lo, hi = S.hi, ak = tlen - plen;
   if (hi - lo + 1 < kPruneLen) return true;
@@ -591,13 +612,14 @@ __device__ __forceinline__ bool wf_prune(const Ring<WIDE>& R, const int plen, co
 
 // One pair on one warp.  Returns score >= 0, OTGPU_SCORE_UNFEASIBLE (-1), or kScoreOverflow
 // (-2, never when WIDE).
-template <int BITS, bool WIDE, bool EF>
-__device__ int wfa_edit_run(const Ring<WIDE>& R, const EditJob& J, const int lane) {
+template <int BITS, int CAP, bool EF>
+__device__ int wfa_edit_run(const Ring<CAP>& R, const EditJob& J, const int lane) {
   const int plen = J.plen, tlen = J.tlen;
   const int cap = R.cap();
   WfState S;
   int s = 0;
 
+  const Grp<32> g(lane);
   // ring invariant: every slot outside the live range [lo,hi] holds a null
   R.fill_null(lane);
   __syncwarp();
@@ -612,36 +634,36 @@ __device__ int wfa_edit_run(const Ring<WIDE>& R, const EditJob& J, const int lan
     for (int k = S.lo + lane; k <= S.hi; k += 32) R.st(k, k > 0 ? k : 0);
   }
   __syncwarp();
-  const LaneConst C(lane);
-  wf_pass<BITS, WIDE, EF, false, true>(R, J, lane, C, S);
+  const LaneConst C(g);
+  wf_pass<BITS, CAP, EF, false, true>(R, J, g, C, S);
   int clo = S.lo, chi = S.hi;  // candidate range the next wf_edges trims
 
   for (;;) {
-    const int st = wf_edges<WIDE, EF>(R, plen, tlen, lane, clo, chi, S);
+    const int st = wf_edges<CAP, EF>(R, plen, tlen, g, clo, chi, S);
     if (st != 0) return st > 0 ? s : -1;  // done | empty wavefront -> WF_STATUS_UNFEASIBLE
     ++s;
     // the pass touches slots [lo-2, hi+1+127] and relies on nulls outside [lo,hi]: no aliasing
-    if (!WIDE && S.hi - S.lo + 136 > cap) return kScoreOverflow;
-    if (WIDE && !EF && S.hi - S.lo + 3 >= kPruneLen) {
+    if (CAP != 0 && S.hi - S.lo + 136 > cap) return kScoreOverflow;
+    if (CAP == 0 && !EF && S.hi - S.lo + 3 >= kPruneLen) {
       // the exact prune sits between compute and extend: run them as separate passes
-      wf_pass<BITS, WIDE, EF, true, false>(R, J, lane, C, S);
-      if (!wf_trim<WIDE>(R, lane, S)) return -1;
-      if (!wf_prune<WIDE>(R, plen, tlen, lane, S)) return -1;
-      wf_pass<BITS, WIDE, EF, false, true>(R, J, lane, C, S);
+      wf_pass<BITS, CAP, EF, true, false>(R, J, g, C, S);
+      if (!wf_trim<CAP>(R, g, S)) return -1;
+      if (!wf_prune<CAP>(R, plen, tlen, lane, S)) return -1;
+      wf_pass<BITS, CAP, EF, false, true>(R, J, g, C, S);
       clo = S.lo;
       chi = S.hi;
     } else {
-      wf_pass<BITS, WIDE, EF, true, true>(R, J, lane, C, S);
+      wf_pass<BITS, CAP, EF, true, true>(R, J, g, C, S);
       clo = S.lo - 1;
       chi = S.hi + 1;
     }
   }
 }
 
-template <int BITS, bool WIDE>
-__device__ __forceinline__ int wfa_edit_pair(const Ring<WIDE>& R, const EditJob& J, const int lane) {
-  return J.pb >= 0 ? wfa_edit_run<BITS, WIDE, true>(R, J, lane)
-                   : wfa_edit_run<BITS, WIDE, false>(R, J, lane);
+template <int BITS, int CAP>
+__device__ __forceinline__ int wfa_edit_pair(const Ring<CAP>& R, const EditJob& J, const int lane) {
+  return J.pb >= 0 ? wfa_edit_run<BITS, CAP, true>(R, J, lane)
+                   : wfa_edit_run<BITS, CAP, false>(R, J, lane);
 }
 
 }  // namespace otgpu

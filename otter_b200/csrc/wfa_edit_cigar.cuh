@@ -89,11 +89,11 @@ __device__ int wfa_editcigar_pair(const AffWork& W, const EditJob& J, const int 
       end_off = tlen;
       goto backtrace;
     }
-    Ring<true> R;
+    Ring<0> R;
     if (S.hi - S.lo + 1 >= kMinWfLen) {
       R.p = cur;
       R.mask = mask;
-      wf_cutoff<true>(R, plen, tlen, lane, dmin, S);
+      wf_cutoff<0>(R, plen, tlen, lane, dmin, S);
     }
 
     // ---- compute score+1 with predecessor choice (wavefront_compute_edit.c:152-195) ----
@@ -131,7 +131,7 @@ __device__ int wfa_editcigar_pair(const AffWork& W, const EditJob& J, const int 
     if (!ef && S.hi - S.lo + 1 >= kPruneLen) {  // exact prune (edit.c:214-269)
       R.p = cur;
       R.mask = mask;
-      if (!wf_prune<true>(R, plen, tlen, lane, S)) return -1;
+      if (!wf_prune<0>(R, plen, tlen, lane, S)) return -1;
     }
   }
 

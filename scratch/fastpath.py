@@ -8,7 +8,7 @@ fn = None; L = []
 for line in txt.splitlines():
     m = re.search(r"Function : (\S+)", line)
     if m: fn = m.group(1); continue
-    if fn and "k_alignILb0" in fn:
+    if fn and "k_alignILi1024" in fn:
         m = re.match(r"\s+/\*([0-9a-f]{4,})\*/\s+(.*?);", line)
         if m: L.append((int(m.group(1), 16), m.group(2).strip()))
 addr = {a: i for i, (a, _) in enumerate(L)}

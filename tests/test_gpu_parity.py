@@ -55,7 +55,18 @@ def test_golden_pairs_through_c_abi(ctx, golden):
     exp = np.array([g["score"] for g in golden["pairs"]], dtype=np.int32)
     assert np.array_equal(got, exp), np.nonzero(got != exp)
     st = ctx.stats()
-    assert st["n_pairs_8bit"] > 0 and st["n_pairs_wide"] > 0  # both fallbacks were exercised
+    assert st["n_pairs_8bit"] > 0  # the raw-byte variant was exercised
+    # the batch holds a 14 kb read, so it ran on the 2048-slot ring; pin the 1024-slot ring to
+    # send the widest pair (1,167 diagonals) through the HBM-ring kernel as well
+    import otter_b200
+    os.environ["OTGPU_RING_SLOTS"] = "1024"
+    try:
+        with otter_b200.Context(0) as c2:
+            got2 = c2.edit_scores(bases, off, lens, PAIRS(rows))
+            assert np.array_equal(got2, exp)
+            assert c2.stats()["n_pairs_wide"] > 0
+    finally:
+        del os.environ["OTGPU_RING_SLOTS"]
 
 
 def test_golden_regions_through_region_abi(ctx, golden):
