@@ -579,6 +579,70 @@ __device__ __forceinline__ int wf_edges(const Ring<CAP>& R, const int plen, cons
   return 0;
 }
 
+// One whole score step for a NARROW wavefront: the computed range [lo-1,hi+1] fits one lane per
+// diagonal, so compute, extend, trim, termination and cut-off all work on registers — one ring
+// load and one store per lane, no probes, no round loop.  Low-error reads (HiFi) spend most of
+// their steps here.  Same order of operations and return value as wf_pass + wf_edges.
+template <int BITS, int CAP, bool EF, int G>
+__device__ __forceinline__ int wf_step_narrow(const Ring<CAP>& R, const EditJob& J, const Grp<G>& g,
+                                              const LaneConst& C, WfState& S) {
+  constexpr int WE = Pack<BITS>::kWin - 1;
+  const int plen = J.plen, tlen = J.tlen, ak = tlen - plen;
+  const int clo = S.lo - 1;  // S.hi + 1 - clo + 1 <= G
+  const int k = clo + g.gl;
+  const int cur = R.ld(k);  // null outside [lo,hi]
+  // ---- compute (wavefront_compute_edit.c:70-97) ----
+  const int left = bitsel(C.mk0, kENull, __shfl_up_sync(g.mask, cur, 1));
+  const int right = bitsel(C.mk31, kENull, __shfl_down_sync(g.mask, cur, 1));
+  int m = max(right, max(left, cur) + 1);
+  const int v = m - k, pr = plen - v, tr = tlen - m, rem = min(pr, tr);
+  const bool ok = (m | v | rem) >= 0;
+  // ---- extend (wavefront_extend.c:203-260) ----
+  int n = (int)min(first_diff<BITS>(J, v, m), (uint32_t)rem);
+  if (__any_sync(g.mask, n == WE)) {
+    const bool c = ok && n == WE && rem > WE;
+    if (__any_sync(g.mask, c)) n = lcp_more<BITS, G>(J, g, v, m, rem, c, n);
+  }
+  m += n;
+  bool fin = false;
+  if (EF) fin = ok && ((tr - n <= 0 && pr - n <= J.pe) || (pr - n <= 0 && tr - n <= J.te));
+  const int sv = ok ? m : kENull;
+  const int dist = plen + max(k, ak) - sv;  // cut-off distance; in the millions for a null
+  R.st(k, sv);
+  __syncwarp(g.mask);
+  // ---- trim (wavefront_compute.c:376-409) ----
+  const unsigned b = __ballot_sync(g.mask, sv >= 0) >> g.first;
+  if (b == 0) return -1;
+  int lo = clo + __ffs(b) - 1, hi = clo + 31 - __clz(b);
+  // ---- termination (wavefront_extend.c:45-68, 122-168) ----
+  const int dm = __reduce_min_sync(g.mask, dist);
+  if (EF ? __any_sync(g.mask, fin) : (dm == 0)) return 1;
+  // ---- WF-adaptive cut-off (wavefront_heuristic.c:285-328) ----
+  if (hi - lo + 1 >= kMinWfLen) {
+    const int dmin = min(max(plen, tlen), dm);
+    const bool keep = dist - dmin <= kMaxDist;
+    const int top = min(ak, hi);
+    int nlo = lo;
+    if (lo < top) {
+      const unsigned b2 = __ballot_sync(g.mask, k >= lo && k < top && keep) >> g.first;
+      nlo = b2 ? clo + __ffs(b2) - 1 : top;
+    }
+    const int bot = max(ak, nlo);
+    int nhi = hi;
+    if (hi > bot) {
+      const unsigned b3 = __ballot_sync(g.mask, k <= hi && k > bot && keep) >> g.first;
+      nhi = b3 ? clo + 31 - __clz(b3) : bot;
+    }
+    if ((k >= lo && k < nlo) || (k <= hi && k > nhi)) R.st(k, kENull);  // ring invariant
+    __syncwarp(g.mask);
+    lo = nlo;
+    hi = nhi;
+  }
+  S.lo = lo;
+  S.hi = hi;
+  return 0;
+}
+
 // Exact prune, end-to-end only, width >= 1000 (wavefront_compute_edit.c:214-269).
 // Returns false if nothing survives (cannot happen: the minimum is attained inside [lo,hi]).
 template <int CAP>
@@ -636,12 +700,14 @@ __device__ int wfa_edit_run(const Ring<CAP>& R, const EditJob& J, const int lane
   __syncwarp();
   const LaneConst C(g);
   wf_pass<BITS, CAP, EF, false, true>(R, J, g, C, S);
-  int clo = S.lo, chi = S.hi;  // candidate range the next wf_edges trims
+  int st = wf_edges<CAP, EF>(R, plen, tlen, g, S.lo, S.hi, S);
 
-  for (;;) {
-    const int st = wf_edges<CAP, EF>(R, plen, tlen, g, clo, chi, S);
-    if (st != 0) return st > 0 ? s : -1;  // done | empty wavefront -> WF_STATUS_UNFEASIBLE
+  while (st == 0) {
     ++s;
+    if (S.hi - S.lo + 3 <= 32) {
+      st = wf_step_narrow<BITS, CAP, EF>(R, J, g, C, S);
+      continue;
+    }
     // the pass touches slots [lo-2, hi+1+127] and relies on nulls outside [lo,hi]: no aliasing
     if (CAP != 0 && S.hi - S.lo + 136 > cap) return kScoreOverflow;
     if (CAP == 0 && !EF && S.hi - S.lo + 3 >= kPruneLen) {
@@ -650,14 +716,13 @@ __device__ int wfa_edit_run(const Ring<CAP>& R, const EditJob& J, const int lane
       if (!wf_trim<CAP>(R, g, S)) return -1;
       if (!wf_prune<CAP>(R, plen, tlen, lane, S)) return -1;
       wf_pass<BITS, CAP, EF, false, true>(R, J, g, C, S);
-      clo = S.lo;
-      chi = S.hi;
+      st = wf_edges<CAP, EF>(R, plen, tlen, g, S.lo, S.hi, S);
     } else {
       wf_pass<BITS, CAP, EF, true, true>(R, J, g, C, S);
-      clo = S.lo - 1;
-      chi = S.hi + 1;
+      st = wf_edges<CAP, EF>(R, plen, tlen, g, S.lo - 1, S.hi + 1, S);
     }
   }
+  return st > 0 ? s : -1;  // done | empty wavefront -> WF_STATUS_UNFEASIBLE
 }
 
 template <int BITS, int CAP>
