@@ -36,6 +36,17 @@ METRIC = "read-pair alignments/sec"
 UNIT = "pairs/s"
 
 
+def load_traffic(workload, n_regions):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture (same workload)."""
+    p = os.path.join(ROOT, "profiles", "r1f_traffic.json")
+    if workload == "C2" and n_regions == synth.CONFIGS["C2"]["n_regions"] and os.path.exists(p):
+        try:
+            return json.load(open(p))["traffic_bytes_per_launch"]
+        except Exception:
+            pass
+    return None
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -411,7 +422,7 @@ def main():
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "k_align<2048>" if B["lens"].max() > 8000 else "k_align<1024>", "achieved": achieved,
                          "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None,
+                         "frac": achieved / peak, "traffic": load_traffic(args.workload, B["n_regions"]),
                          "alg_bytes_per_launch": B["alg_bytes"], "kernel_ms": k_ms,
                          "note": "latency/issue-bound integer DP: HBM fraction is expected to be "
                                  "tiny; see profiles/ for issue-slot and stall evidence"},
