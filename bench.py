@@ -278,6 +278,80 @@ def run_consensus(args, rank, world, local_rank):
     ctx.close()
 
 
+def run_compare(args, rank, world, local_rank):
+    """Secondary measurement (BASELINE.json configs[4]): all-pairs allele x allele
+    edit distance with CIGAR length, as `otter compare`'s get_distances computes it
+    (src/compare.cpp:50-66).  Per region a cohort of assembled alleles (two true alleles, consensus-
+    grade error 0.1 %); every pair (longer, shorter) end-to-end."""
+    import ctypes as C
+    n_regions = args.regions or 16
+    n_alleles = 200
+    rng = np.random.default_rng(0xC5 + rank)
+    reads, rows = [], []
+    for _ in range(n_regions):
+        tl = int(rng.integers(2000, 5001))
+        reg = synth.tr_region(rng, n_alleles, tl, 0.001, n_rate=0.0)
+        base = len(reads)
+        reads += reg
+        ln = np.array([len(r) for r in reg])
+        i, j = np.triu_indices(n_alleles, 1)
+        swap = ln[i] < ln[j]
+        a = np.where(swap, j, i) + base
+        b = np.where(swap, i, j) + base
+        rows.append(np.stack([a, b, np.full_like(a, -1), 0 * a, 0 * a, 0 * a], axis=1))
+    req = np.concatenate(rows).astype(np.int32)
+    bases, off, lens = synth.pack_reads(reads)
+    n = len(req)
+    line = {"metric": "allele-pair edit-distance+CIGAR-length alignments/sec", "unit": "alignments/s",
+            "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "higher_is_better": True,
+            "dtype": "int32", "data": "synthetic",
+            "config": {"workload": f"C5-shaped: {n_regions} regions x {n_alleles} alleles of 2-5 kb, "
+                                   f"all pairs per region ({n} alignments)", "regions": n_regions}}
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        lib = C.CDLL(os.path.join(ROOT, "oracle", "_ref", "libotter_ref.so"))
+        lib.ref_edit_cigars_batch.restype = C.c_double
+        threads = os.cpu_count() or 1
+        vp = C.c_void_p
+        m = min(n, 40000)  # bounded sample
+        clen = np.zeros(m, dtype=np.int32)
+        t = 0.0
+        for _ in range(args.steps):
+            t += lib.ref_edit_cigars_batch(bases.ctypes.data_as(vp), off.ctypes.data_as(vp),
+                                           lens.ctypes.data_as(vp), req[:m].ctypes.data_as(vp),
+                                           C.c_uint64(m), threads, clen.ctypes.data_as(vp))
+        line.update(impl="reference", value=m * args.steps / t, ms_per_step=1e3 * t / args.steps,
+                    cpu_baseline={"kind": "reference", "cores": threads, "value": m * args.steps / t,
+                                  "unit": "alignments/s", "sample": f"first {m} of {n} alignments"})
+        print(json.dumps(line), flush=True)
+        return
+    import otter_b200
+    from otter_b200.capi import PAIR_DTYPE
+    pairs = np.zeros(n, dtype=PAIR_DTYPE)
+    for i, f in enumerate(("pattern", "text", "pbf", "pef", "tbf", "tef")):
+        pairs[f] = req[:, i]
+    ctx = otter_b200.Context(local_rank)
+    for _ in range(max(args.warmup, 1)):
+        scores, clen = ctx.edit_cigar_lengths(bases, off, lens, pairs)
+    l0 = ctx.stats()["kernel_launches"]
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        scores, clen = ctx.edit_cigar_lengths(bases, off, lens, pairs)
+    t = time.perf_counter() - t0
+    line.update(value=n * args.steps / t, ms_per_step=1e3 * t / args.steps,
+                gpu_launches=int(ctx.stats()["kernel_launches"] - l0),
+                e2e={"value": n * args.steps / t, "unit": "alignments/s",
+                     "h2d_bytes_per_step": int(bases.nbytes + pairs.nbytes),
+                     "d2h_bytes_per_step": int(scores.nbytes + clen.nbytes)},
+                retried=int(ctx.stats()["n_pairs_wide"]),
+                checksum=[int(scores.astype(np.int64).sum()), int(clen.astype(np.int64).sum())],
+                note="host buffers -> otgpu_edit_cigars (scores + CIGAR lengths only) -> host, wall clock")
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    ctx.close()
+
+
 # ------------------------------------------------------------------------------------------------
 def main():
     ap = argparse.ArgumentParser()
@@ -288,7 +362,7 @@ def main():
     ap.add_argument("--regions", type=int, default=None, help="override regions per GPU")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--path", default="distmatrix", choices=["distmatrix", "consensus"],
+    ap.add_argument("--path", default="distmatrix", choices=["distmatrix", "consensus", "compare"],
                     help="distmatrix = fill_dist_matrix (the headline); consensus = the gap-affine "
                          "+ CIGAR alignments rapid_consensus issues (secondary row)")
     args = ap.parse_args()
@@ -300,6 +374,9 @@ def main():
 
     if args.path == "consensus":
         run_consensus(args, rank, world, local_rank)
+        return
+    if args.path == "compare":
+        run_compare(args, rank, world, local_rank)
         return
     if args.impl == "reference":
         run_reference(args, rank, world)

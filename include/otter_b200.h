@@ -141,7 +141,9 @@ int otgpu_affine_cigars(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
  * MemoryMed), alignEnd2End + getAlignmentScore + getAlignmentCigar): same wavefronts, heuristic
  * and exact prune as otgpu_edit_scores, plus the CIGAR (ties mismatch > deletion > insertion,
  * wavefront_compute_edit.c:152-195; linear unpack, wavefront_backtrace_buffer.c:266-312).
- * Arguments and outputs as otgpu_affine_cigars; scores_out[i] = the edit score. */
+ * Arguments and outputs as otgpu_affine_cigars; scores_out[i] = the edit score.
+ * For both functions cigars_out = cigar_off = NULL asks for scores and CIGAR lengths only
+ * (what get_distances uses, src/compare.cpp:60-61): no CIGAR bytes are written or copied. */
 int otgpu_edit_cigars(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
                       const uint64_t* read_off, const uint32_t* read_len, uint32_t n_reads,
                       const otgpu_pair* pairs, uint64_t n_pairs, int32_t* scores_out,

@@ -304,15 +304,29 @@ int ref_assemble_region(const char* bases, const uint64_t* off, const uint32_t* 
 // contiguous blocks over `threads` workers, one WFAlignerGapAffine(4,6,2,Alignment,MemoryMed)
 // each.  pairs = 6 int32 per request (pattern read, text read, pb, pe, tb, te).  Returns wall
 // seconds; cigar_len[i] = length of request i's CIGAR (the strings themselves are dropped).
+double ref_cigars_batch_impl(bool edit, const char* bases, const uint64_t* off, const uint32_t* len,
+                             const int32_t* pairs, uint64_t n_pairs, int threads, int32_t* cigar_len);
 double ref_affine_cigars_batch(const char* bases, const uint64_t* off, const uint32_t* len,
                                const int32_t* pairs, uint64_t n_pairs, int threads,
                                int32_t* cigar_len) {
+  return ref_cigars_batch_impl(false, bases, off, len, pairs, n_pairs, threads, cigar_len);
+}
+// The same with compare's aligner (WFAlignerEdit(Alignment, MemoryMed), src/compare.cpp:95).
+double ref_edit_cigars_batch(const char* bases, const uint64_t* off, const uint32_t* len,
+                             const int32_t* pairs, uint64_t n_pairs, int threads,
+                             int32_t* cigar_len) {
+  return ref_cigars_batch_impl(true, bases, off, len, pairs, n_pairs, threads, cigar_len);
+}
+double ref_cigars_batch_impl(bool edit, const char* bases, const uint64_t* off, const uint32_t* len,
+                             const int32_t* pairs, uint64_t n_pairs, int threads, int32_t* cigar_len) {
   if (threads < 1) threads = 1;
   auto t0 = std::chrono::steady_clock::now();
   std::vector<std::thread> pool;
   for (int t = 0; t < threads; ++t) {
     pool.emplace_back([&, t]() {
-      wfa::WFAlignerGapAffine a(4, 6, 2, wfa::WFAligner::Alignment, wfa::WFAligner::MemoryMed);
+      wfa::WFAlignerGapAffine aff(4, 6, 2, wfa::WFAligner::Alignment, wfa::WFAligner::MemoryMed);
+      wfa::WFAlignerEdit ed(wfa::WFAligner::Alignment, wfa::WFAligner::MemoryMed);
+      wfa::WFAligner& a = edit ? static_cast<wfa::WFAligner&>(ed) : static_cast<wfa::WFAligner&>(aff);
       const uint64_t lo = n_pairs * t / threads, hi = n_pairs * (t + 1) / threads;
       for (uint64_t i = lo; i < hi; ++i) {
         const int32_t* q = pairs + 6 * i;

@@ -156,6 +156,16 @@ class Context:
         """Edit distance with CIGAR (compare's aligner) -> (scores, CIGAR bytes | status)."""
         return self.affine_cigars(bases, off, lens, pairs, edit=True)
 
+    def edit_cigar_lengths(self, bases, off, lens, pairs, scores=None, clen=None):
+        """Scores and CIGAR lengths only (what get_distances uses): no CIGAR bytes leave the GPU."""
+        pairs = np.ascontiguousarray(pairs, dtype=PAIR_DTYPE)
+        n = len(pairs)
+        scores = np.zeros(n, dtype=np.int32) if scores is None else scores
+        clen = np.zeros(n, dtype=np.int32) if clen is None else clen
+        self._ck(self._l.otgpu_edit_cigars(self._h, _p(bases), bases.size, _p(off), _p(lens), len(lens),
+                                           _p(pairs), n, _p(scores), None, None, _p(clen)))
+        return scores, clen
+
     def affine_cigars(self, bases, off, lens, pairs, x=4, o=6, e=2, edit=False):
         """-> (scores int32[n], list of CIGAR bytes or negative status ints)."""
         pairs = np.ascontiguousarray(pairs, dtype=PAIR_DTYPE)

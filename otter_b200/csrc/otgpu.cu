@@ -683,8 +683,9 @@ k_affine(DevBatch b, Counters* __restrict__ ctr, uint32_t* __restrict__ ovf_list
     J.pb = pr.pattern_begin_free; J.pe = pr.pattern_end_free;
     J.tb = pr.text_begin_free;    J.te = pr.text_end_free;
     const bool bytes = ((b.read_flag[pr.pattern] | b.read_flag[pr.text]) & 1u) != 0;
-    const uint64_t c0 = cigar_off[idx];
-    const int cap = (int)(cigar_off[idx + 1] - c0);
+    // cigar_off == nullptr: the caller wants scores and CIGAR lengths only, nothing is written
+    const uint64_t c0 = cigar_off ? cigar_off[idx] : 0;
+    const int cap = cigar_off ? (int)(cigar_off[idx + 1] - c0) : 0;
     int score = 0, len;
     if (bytes) {
       J.words = reinterpret_cast<const uint32_t*>(b.bases);
@@ -720,12 +721,13 @@ int cigars_impl(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const ui
                 const uint32_t* read_len, uint32_t n_reads, const otgpu_pair* pairs,
                 uint64_t n_pairs, const bool edit, AffPen pen, int32_t* scores_out, char* cigars_out,
                 const uint64_t* cigar_off, int32_t* cigar_len_out) {
-  if (!ctx || ((!scores_out || !cigar_off || !cigar_len_out) && n_pairs)) return OTGPU_ERR_ARGS;
+  if (!ctx || ((!scores_out || !cigar_len_out) && n_pairs)) return OTGPU_ERR_ARGS;
+  if (!cigar_off && cigars_out) return OTGPU_ERR_ARGS;  // both null = lengths only
   int s = otgpu_batch_upload_pairs(ctx, bases, n_bases, read_off, read_len, n_reads, pairs, n_pairs);
   if (s != OTGPU_OK) return s;
   if (n_pairs == 0) return OTGPU_OK;
-  const uint64_t cig_bytes = cigar_off[n_pairs];
-  for (uint64_t i = 0; i < n_pairs; ++i)
+  const uint64_t cig_bytes = cigar_off ? cigar_off[n_pairs] : 0;
+  for (uint64_t i = 0; cigar_off && i < n_pairs; ++i)
     if (cigar_off[i + 1] < cigar_off[i]) return OTGPU_ERR_ARGS;
   if (cig_bytes && !cigars_out) return OTGPU_ERR_ARGS;
   CK(cudaSetDevice(ctx->device));
@@ -734,8 +736,10 @@ int cigars_impl(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const ui
   const int wcap = next_pow2(2 * (int)ctx->max_len + 64);
   const uint32_t ops_cap = 4u * ctx->max_len + 64u;
   const size_t ring_bytes = (size_t)(edit ? 2 : 3 * pen.scope) * wcap * 4;
-  const uint32_t slab1 = 2u << 20;
-  int grid = ctx->n_sm * 1;
+  // first-tier trace slab per warp: edit distance stores one byte per (score, diagonal) of ONE
+  // component and its wavefronts are narrower, so half the slab and four times the warps
+  const uint32_t slab1 = edit ? (1u << 20) : (2u << 20);
+  int grid = ctx->n_sm * (edit ? 4 : 1);
   while (grid > 8 && (size_t)grid * kWarpsPerCta * (ring_bytes + slab1 + ops_cap) > ((size_t)24 << 30)) grid /= 2;
   const size_t nw = (size_t)grid * kWarpsPerCta;
   RS(aff_rings, nw * ring_bytes);
@@ -744,7 +748,9 @@ int cigars_impl(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const ui
   RS(cigar_off, (n_pairs + 1) * 8);
   RS(cigars, cig_bytes + 16);
   RS(cigar_len, n_pairs * 4);
-  CK(cudaMemcpyAsync(ctx->cigar_off.p, cigar_off, (n_pairs + 1) * 8, cudaMemcpyHostToDevice, st));
+  if (cigar_off)
+    CK(cudaMemcpyAsync(ctx->cigar_off.p, cigar_off, (n_pairs + 1) * 8, cudaMemcpyHostToDevice, st));
+  const uint64_t* d_cigar_off = cigar_off ? static_cast<const uint64_t*>(ctx->cigar_off.p) : nullptr;
   DevBatch b;
   b.bases = static_cast<const uint8_t*>(ctx->bases.p);
   b.read_off = static_cast<const uint64_t*>(ctx->read_off.p);
@@ -764,8 +770,7 @@ int cigars_impl(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const ui
   (edit ? k_affine<false, true> : k_affine<false, false>)<<<grid, kCtaThreads, 0, st>>>(
       b, ctr, ovf, pen, static_cast<int32_t*>(ctx->aff_rings.p), wcap,
       static_cast<uint8_t*>(ctx->aff_slab.p), slab1, static_cast<uint8_t*>(ctx->aff_ops.p), ops_cap,
-      static_cast<const uint64_t*>(ctx->cigar_off.p), static_cast<char*>(ctx->cigars.p),
-      static_cast<int32_t*>(ctx->cigar_len.p));
+      d_cigar_off, static_cast<char*>(ctx->cigars.p), static_cast<int32_t*>(ctx->cigar_len.p));
   ctx->stats.kernel_launches += 2;
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(ctx->h_counters, ctx->counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, st));
@@ -779,7 +784,7 @@ int cigars_impl(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const ui
     (edit ? k_affine<true, true> : k_affine<true, false>)<<<grid2, kCtaThreads, 0, st>>>(
         b, ctr, ovf, pen, static_cast<int32_t*>(ctx->aff_rings.p), wcap,
         static_cast<uint8_t*>(ctx->aff_slab2.p), slab2, static_cast<uint8_t*>(ctx->aff_ops.p),
-        ops_cap, static_cast<const uint64_t*>(ctx->cigar_off.p), static_cast<char*>(ctx->cigars.p),
+        ops_cap, d_cigar_off, static_cast<char*>(ctx->cigars.p),
         static_cast<int32_t*>(ctx->cigar_len.p));
     ctx->stats.kernel_launches++;
     CK(cudaGetLastError());

@@ -55,9 +55,11 @@ void affine_cigars(wfa::WFAligner& aligner2, const std::vector<CigarJob>& jobs,
 
 // The same for either aligner flavour that produces CIGARs: gap-affine (aligner2) or edit
 // distance with CIGAR (`compare`'s WFAlignerEdit(Alignment), src/compare.cpp:95).
-// scores_out (optional) receives getAlignmentScore() per job.
+// Each output is optional: cigars (the strings), scores_out (getAlignmentScore()), lengths_out
+// (getAlignmentCigar().size()).  With cigars == nullptr no CIGAR bytes leave the device.
 void batched_cigars(wfa::WFAligner& aligner, const std::vector<CigarJob>& jobs,
-                    std::vector<std::string>& cigars, std::vector<int>* scores_out);
+                    std::vector<std::string>* cigars, std::vector<int>* scores_out,
+                    std::vector<int>* lengths_out);
 
 // local_realignment (src/analignments.cpp:11-60) with the two reference flanks already fetched
 // (ref_left = ref[start-flank,start), ref_right = ref[end,end+flank), upper-cased as

@@ -30,13 +30,12 @@ void get_distances_batch(wfa::WFAligner& aligner, std::vector<CompareJob>& jobs)
       }
     }
   }
-  std::vector<std::string> cigars;
-  std::vector<int> scores;
-  batched_cigars(aligner, work, cigars, &scores);
+  std::vector<int> scores, lengths;  // the CIGAR itself is not used, only its length
+  batched_cigars(aligner, work, nullptr, &scores, &lengths);
   for (size_t w = 0; w < work.size(); ++w) {
     DistCompare& d = (*jobs[slots[w].job].distances)[slots[w].at];
-    d.edit = scores[w];                // getAlignmentScore()          (:60)
-    d.ops = (double)cigars[w].size();  // getAlignmentCigar().size()   (:61)
+    d.edit = scores[w];   // getAlignmentScore()          (:60)
+    d.ops = lengths[w];   // getAlignmentCigar().size()   (:61)
   }
 }
 

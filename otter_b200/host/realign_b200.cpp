@@ -25,14 +25,16 @@ namespace {
 // -------------------------------------------------------------------------------------------------
 void affine_cigars(wfa::WFAligner& aligner2, const std::vector<CigarJob>& jobs,
                    std::vector<std::string>& cigars) {
-  batched_cigars(aligner2, jobs, cigars, nullptr);
+  batched_cigars(aligner2, jobs, &cigars, nullptr, nullptr);
 }
 
 // Gap-affine aligner -> otgpu_affine_cigars; edit aligner (compare's) -> otgpu_edit_cigars.
 void batched_cigars(wfa::WFAligner& aligner2, const std::vector<CigarJob>& jobs,
-                    std::vector<std::string>& cigars, std::vector<int>* scores_out) {
-  cigars.assign(jobs.size(), std::string());
+                    std::vector<std::string>* cigars, std::vector<int>* scores_out,
+                    std::vector<int>* lengths_out) {
+  if (cigars) cigars->assign(jobs.size(), std::string());
   if (scores_out) scores_out->assign(jobs.size(), 0);
+  if (lengths_out) lengths_out->assign(jobs.size(), 0);
   if (jobs.empty()) return;
   otgpu_ctx* ctx = aligner2.context();
   if (!ctx) die("affine_cigars", OTGPU_ERR_NO_DEVICE, nullptr);
@@ -72,20 +74,21 @@ void batched_cigars(wfa::WFAligner& aligner2, const std::vector<CigarJob>& jobs,
     coff[i + 1] = coff[i] + j.pattern->size() + j.text->size();  // a CIGAR is never longer
   }
   std::vector<int32_t> scores(jobs.size()), clen(jobs.size());
-  std::vector<char> cig(coff.back() + 1);
+  std::vector<char> cig(cigars ? coff.back() + 1 : 1);  // no CIGAR bytes when only lengths are wanted
+  char* cig_ptr = cigars ? cig.data() : nullptr;
+  const uint64_t* coff_ptr = cigars ? coff.data() : nullptr;
   st = aligner2.isEdit()
       ? otgpu_edit_cigars(ctx, bases, used, off.data(), len.data(), (uint32_t)order.size(),
-                          pairs.data(), pairs.size(), scores.data(), cig.data(), coff.data(),
-                          clen.data())
+                          pairs.data(), pairs.size(), scores.data(), cig_ptr, coff_ptr, clen.data())
       : otgpu_affine_cigars(ctx, bases, used, off.data(), len.data(), (uint32_t)order.size(),
                             pairs.data(), pairs.size(), aligner2.mismatch(), aligner2.gapOpening(),
-                            aligner2.gapExtension(), scores.data(), cig.data(), coff.data(),
-                            clen.data());
+                            aligner2.gapExtension(), scores.data(), cig_ptr, coff_ptr, clen.data());
   otgpu_host_free(pinned);
   if (st != OTGPU_OK) die("batched_cigars", st, ctx);
   for (size_t i = 0; i < jobs.size(); ++i) {
-    if (clen[i] >= 0) cigars[i].assign(cig.data() + coff[i], (size_t)clen[i]);
+    if (cigars && clen[i] >= 0) (*cigars)[i].assign(cig.data() + coff[i], (size_t)clen[i]);
     if (scores_out) (*scores_out)[i] = scores[i];
+    if (lengths_out) (*lengths_out)[i] = clen[i] >= 0 ? clen[i] : 0;
   }
   // clen < 0 (unfeasible / OOM): the reference ignores the status and reads whatever CIGAR the
   // aligner holds; an empty string is the closest defined behaviour and is not reachable for the

@@ -88,6 +88,9 @@ def test_edit_cigars_vs_port_random(ctx):
     pairs = PAIRS(rows)
     scores, cigs = ctx.edit_cigars(bases, off, lens, pairs)
     so = ctx.edit_scores(bases, off, lens, pairs)
+    sc_only, len_only = ctx.edit_cigar_lengths(bases, off, lens, pairs)  # no CIGAR bytes requested
+    assert np.array_equal(sc_only, scores)
+    assert len_only.tolist() == [len(c) for c in cigs]
     for r, sc, cg, s2 in zip(rows, scores, cigs, so):
         p, t = S.b(reads[r[0]]), S.b(reads[r[1]])
         ef = r[2] >= 0
