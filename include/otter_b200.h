@@ -100,6 +100,12 @@ int otgpu_region_edit_scores(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_ba
                              const uint64_t* read_off, const uint32_t* read_len,
                              uint32_t n_reads, const uint32_t* region_start, uint32_t n_regions,
                              const uint64_t* score_off, uint64_t n_scores, int32_t* scores_out);
+/* Batches larger than ~1.5 x 256 MB of reads (laid out region after region, as above) are streamed
+ * through two sets of device buffers in chunks of consecutive regions, so that the upload of one
+ * chunk overlaps the alignment of the previous one and device memory stays bounded; scores are
+ * identical to a single batch.  Number of chunks the last otgpu_region_edit_scores call used: */
+uint64_t otgpu_last_chunk_count(const otgpu_ctx* ctx);
+
 
 /* ---- split-phase calls (inputs stay resident in HBM between phases) ---------------------- */
 /* upload: async H2D of the batch on ctx's stream.  align: pack + pair expansion + alignment

@@ -14,7 +14,7 @@ SYMBOLS = [
     "otgpu_host_free", "otgpu_edit_scores", "otgpu_region_edit_scores",
     "otgpu_batch_upload_regions", "otgpu_batch_upload_pairs", "otgpu_batch_align",
     "otgpu_batch_download", "otgpu_synchronize", "otgpu_last_align_ms", "otgpu_affine_cigars",
-    "otgpu_edit_cigars",
+    "otgpu_edit_cigars", "otgpu_last_chunk_count",
 ]
 
 
@@ -74,6 +74,8 @@ def lib():
         l.otgpu_last_align_ms.argtypes = [vp, C.POINTER(C.c_float * 4)]
         l.otgpu_affine_cigars.argtypes = [vp, vp, u64, vp, vp, u32, vp, u64, i32, i32, i32, vp, vp, vp, vp]
         l.otgpu_edit_cigars.argtypes = [vp, vp, u64, vp, vp, u32, vp, u64, vp, vp, vp, vp]
+        l.otgpu_last_chunk_count.restype = u64
+        l.otgpu_last_chunk_count.argtypes = [vp]
         _lib = l
     return _lib
 
@@ -151,6 +153,9 @@ class Context:
                                                   len(lens), _p(region_start), len(region_start) - 1,
                                                   _p(score_off), n_scores, _p(out)))
         return out
+
+    def last_chunk_count(self):
+        return int(self._l.otgpu_last_chunk_count(self._h))
 
     def edit_cigars(self, bases, off, lens, pairs):
         """Edit distance with CIGAR (compare's aligner) -> (scores, CIGAR bytes | status)."""

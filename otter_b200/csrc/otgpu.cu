@@ -18,6 +18,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <vector>
 
 using namespace otgpu;
 
@@ -238,6 +239,11 @@ struct otgpu_ctx {
   uint32_t n_reads = 0, n_regions = 0, max_len = 0;
   int grid_main = 0, grid_main_long = 0, grid_wide = 0, wide_cap = 0, wide_per_sm = 2;
   int force_ring = 0;  // OTGPU_RING_SLOTS=1024|2048 at otgpu_create: pin the ring tier (tests)
+  // streaming of large region batches (otgpu_region_edit_scores): a second context on the same
+  // device, made on first use, so that chunk i+1 uploads while chunk i aligns
+  otgpu_ctx* peer = nullptr;
+  uint64_t chunk_bases = (uint64_t)256 << 20;  // OTGPU_CHUNK_MB at otgpu_create (tests use 1)
+  uint64_t n_chunks_last = 0;
   otgpu_stats stats = {0, 0, 0, 0};
   cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // pack|expand|align|wide|end
   bool timed = false;
@@ -402,6 +408,10 @@ int otgpu_create(int device, otgpu_ctx** out) {
     const int v = atoi(rs);
     if (v == 1024 || v == 2048) ctx->force_ring = v;
   }
+  if (const char* cm = getenv("OTGPU_CHUNK_MB")) {
+    const long v = atol(cm);
+    if (v > 0) ctx->chunk_bases = (uint64_t)v << 20;
+  }
   cudaError_t e = cudaSetDevice(device);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaDeviceGetAttribute(&ctx->n_sm, cudaDevAttrMultiProcessorCount, device);
@@ -417,6 +427,7 @@ int otgpu_create(int device, otgpu_ctx** out) {
 
 void otgpu_destroy(otgpu_ctx* ctx) {
   if (!ctx) return;
+  if (ctx->peer) otgpu_destroy(ctx->peer);
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   DevBuf* bufs[] = {&ctx->bases, &ctx->read_off, &ctx->read_len, &ctx->pk_off, &ctx->read_flag,
@@ -436,6 +447,8 @@ void otgpu_destroy(otgpu_ctx* ctx) {
 
 const char* otgpu_last_cuda_error(const otgpu_ctx* ctx) { return ctx ? ctx->err : ""; }
 void* otgpu_stream(otgpu_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+uint64_t otgpu_last_chunk_count(const otgpu_ctx* ctx) { return ctx ? ctx->n_chunks_last : 0; }
 
 int otgpu_get_stats(const otgpu_ctx* ctx, otgpu_stats* out) {
   if (!ctx || !out) return OTGPU_ERR_ARGS;
@@ -636,10 +649,110 @@ int otgpu_edit_scores(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
   return s;
 }
 
+// Large batches are streamed: consecutive regions are cut into chunks of about chunk_bases bytes
+// of reads and the chunks alternate between two contexts (two streams, two sets of buffers) on the
+// same device, so the H2D copy and the host-side table building of chunk i+1 overlap the kernels
+// of chunk i, and device memory stays bounded by two chunks.  Requires the usual layout (reads and
+// scores of consecutive regions are consecutive); anything else takes the single-batch path.
+// Results do not depend on the chunking (regions are independent).
+static int region_scores_streamed(otgpu_ctx* ctx, const uint8_t* bases, const uint64_t* read_off,
+                                  const uint32_t* read_len, const uint32_t* region_start,
+                                  uint32_t n_regions, const uint64_t* score_off,
+                                  int32_t* scores_out) {
+  if (!ctx->peer) {
+    const int s = otgpu_create(ctx->device, &ctx->peer);
+    if (s != OTGPU_OK) return s;
+    ctx->peer->force_ring = ctx->force_ring;
+  }
+  otgpu_ctx* slot[2] = {ctx, ctx->peer};
+  struct Pending { bool on = false; uint64_t s0 = 0, ns = 0; } pend[2];
+  std::vector<uint64_t> off_c, so_c;
+  std::vector<uint32_t> rs_c;
+  uint64_t chunks = 0, pairs_total = 0, wide_total = 0, b8_total = 0;
+  auto finish = [&](int k) -> int {
+    if (!pend[k].on) return OTGPU_OK;
+    pend[k].on = false;
+    const int s = otgpu_batch_download(slot[k], scores_out + pend[k].s0, pend[k].ns);
+    pairs_total += slot[k]->stats.n_pairs;
+    wide_total += slot[k]->stats.n_pairs_wide;
+    b8_total += slot[k]->stats.n_pairs_8bit;
+    if (k == 1) ctx->stats.kernel_launches += slot[1]->stats.kernel_launches, slot[1]->stats.kernel_launches = 0;
+    return s;
+  };
+  uint32_t g0 = 0;
+  while (g0 < n_regions) {
+    uint32_t g1 = g0;
+    const uint64_t base0 = read_off[region_start[g0]];
+    uint64_t bytes = 0;
+    while (g1 < n_regions && (g1 == g0 || bytes < ctx->chunk_bases)) {
+      const uint32_t ra = region_start[g1], rb = region_start[g1 + 1];
+      if (rb > ra) bytes = read_off[rb - 1] + read_len[rb - 1] - base0;
+      ++g1;
+    }
+    const uint32_t r0 = region_start[g0], r1 = region_start[g1];
+    const uint64_t s0 = score_off[g0];
+    off_c.resize(r1 - r0);
+    for (uint32_t r = r0; r < r1; ++r) off_c[r - r0] = read_off[r] - base0;
+    rs_c.resize(g1 - g0 + 1);
+    so_c.resize(g1 - g0);
+    uint64_t ns = 0;
+    for (uint32_t g = g0; g < g1; ++g) {
+      rs_c[g - g0] = region_start[g] - r0;
+      so_c[g - g0] = score_off[g] - s0;
+      const uint64_t n = region_start[g + 1] - region_start[g];
+      ns = so_c[g - g0] + n * (n ? n - 1 : 0) / 2;
+    }
+    rs_c[g1 - g0] = r1 - r0;
+    const int k = (int)(chunks & 1);
+    int s = finish(k);  // the chunk before last on this slot: its buffers are about to be reused
+    if (s == OTGPU_OK)
+      s = otgpu_batch_upload_regions(slot[k], bases + base0, bytes, off_c.data(), read_len + r0, r1 - r0,
+                                     rs_c.data(), g1 - g0, so_c.data(), ns);
+    if (s == OTGPU_OK) s = otgpu_batch_align(slot[k]);
+    if (s != OTGPU_OK) {
+      if (k == 1) snprintf(ctx->err, sizeof(ctx->err), "%s", slot[1]->err);
+      return s;
+    }
+    pend[k].on = true;
+    pend[k].s0 = s0;
+    pend[k].ns = ns;
+    ++chunks;
+    g0 = g1;
+  }
+  int s = finish((int)(chunks & 1));
+  if (s == OTGPU_OK) s = finish((int)((chunks + 1) & 1));
+  ctx->stats.n_pairs = pairs_total;
+  ctx->stats.n_pairs_wide = wide_total;
+  ctx->stats.n_pairs_8bit = b8_total;
+  ctx->n_chunks_last = chunks;
+  return s;
+}
+
 int otgpu_region_edit_scores(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
                              const uint64_t* read_off, const uint32_t* read_len,
                              uint32_t n_reads, const uint32_t* region_start, uint32_t n_regions,
                              const uint64_t* score_off, uint64_t n_scores, int32_t* scores_out) {
+  if (ctx) ctx->n_chunks_last = 1;
+  if (ctx && bases && read_off && read_len && region_start && score_off && scores_out &&
+      n_regions > 1 && n_bases > ctx->chunk_bases + ctx->chunk_bases / 2) {
+    // streaming needs reads and scores laid out region after region, which is how every caller
+    // here builds them; verify, else fall through to the single batch
+    bool ok = region_start[0] == 0 && region_start[n_regions] == n_reads && score_off[0] == 0;
+    uint64_t at = 0, sc = 0;
+    for (uint32_t g = 0; ok && g < n_regions; ++g) {
+      if (region_start[g + 1] < region_start[g] || region_start[g + 1] > n_reads) { ok = false; break; }
+      const uint64_t n = region_start[g + 1] - region_start[g];
+      ok = score_off[g] == sc;
+      sc += n * (n ? n - 1 : 0) / 2;
+      for (uint32_t r = region_start[g]; ok && r < region_start[g + 1]; ++r) {
+        ok = read_off[r] >= at && read_off[r] + read_len[r] <= n_bases;
+        at = read_off[r] + read_len[r];
+      }
+    }
+    if (ok && sc == n_scores)
+      return region_scores_streamed(ctx, bases, read_off, read_len, region_start, n_regions, score_off,
+                                    scores_out);
+  }
   int s = otgpu_batch_upload_regions(ctx, bases, n_bases, read_off, read_len, n_reads,
                                      region_start, n_regions, score_off, n_scores);
   if (s == OTGPU_OK) s = otgpu_batch_align(ctx);

@@ -281,3 +281,28 @@ def test_host_layer_batched_equals_per_region(built):
 def test_smoke_entry(built):
     import __graft_entry__ as g
     g.smoke()
+
+
+def test_streamed_chunks_equal_single_batch(ctx):
+    """otgpu_region_edit_scores streams large batches in chunks over two buffer sets; with the
+    chunk size forced down to 1 MB a 3 MB batch must take several chunks and give the same scores."""
+    import otter_b200
+    rng = np.random.default_rng(404)
+    regions = [S.tr_region(rng, 12, int(rng.integers(1500, 4000)), 0.03, extra_frac=0.2) for _ in range(90)]
+    regions.insert(7, [])            # an empty region and a single-read region inside a chunk
+    regions.insert(30, regions[3][:1])
+    B = S.region_batch(regions)
+    assert B["bases"].size > 2_500_000
+    exp = ctx.region_edit_scores(B["bases"], B["off"], B["lens"], B["region_start"], B["score_off"], B["n_scores"])
+    assert ctx.last_chunk_count() == 1
+    os.environ["OTGPU_CHUNK_MB"] = "1"
+    try:
+        with otter_b200.Context(0) as c2:
+            for _ in range(2):  # second call reuses both buffer sets
+                got = c2.region_edit_scores(B["bases"], B["off"], B["lens"], B["region_start"],
+                                            B["score_off"], B["n_scores"])
+                assert c2.last_chunk_count() >= 3
+                assert np.array_equal(got, exp)
+                assert c2.stats()["n_pairs"] == B["n_scores"]
+    finally:
+        del os.environ["OTGPU_CHUNK_MB"]
