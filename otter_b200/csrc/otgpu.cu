@@ -852,7 +852,11 @@ int cigars_impl(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const ui
   // first-tier trace slab per warp: edit distance stores one byte per (score, diagonal) of ONE
   // component and its wavefronts are narrower, so half the slab and four times the warps
   const uint32_t slab1 = edit ? (1u << 20) : (2u << 20);
-  int grid = ctx->n_sm * (edit ? 4 : 1);
+  int per_sm = 1;  // latency-bound on its per-warp HBM rings: as many resident warps as fit
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+      &per_sm, edit ? k_affine<false, true> : k_affine<false, false>, kCtaThreads, 0));
+  if (const char* e = getenv("OTGPU_AFF_CTAS")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;
+  int grid = ctx->n_sm * (per_sm > 0 ? per_sm : 1);
   while (grid > 8 && (size_t)grid * kWarpsPerCta * (ring_bytes + slab1 + ops_cap) > ((size_t)24 << 30)) grid /= 2;
   const size_t nw = (size_t)grid * kWarpsPerCta;
   RS(aff_rings, nw * ring_bytes);
@@ -920,8 +924,12 @@ extern "C" int otgpu_affine_cigars(otgpu_ctx* ctx, const uint8_t* bases, uint64_
                                    int32_t* cigar_len_out) {
   // wavefronts_penalties_set_affine (wavefront_penalties.c:86-119): X>0, O>=0, E>0
   if (mismatch <= 0 || gap_open < 0 || gap_ext <= 0) return OTGPU_ERR_ARGS;
-  AffPen pen{mismatch, gap_open, gap_ext, 0};
+  AffPen pen{mismatch, gap_open, gap_ext, 0, 1};
   pen.scope = (gap_open + gap_ext > mismatch ? gap_open + gap_ext : mismatch) + 1;
+  {
+    auto gcd = [](int a, int b) { while (b) { const int t = a % b; a = b; b = t; } return a; };
+    pen.step = gcd(gcd(mismatch, gap_open + gap_ext), gap_ext);
+  }
   if (pen.scope > kAffMaxScope) return OTGPU_ERR_ARGS;
   return cigars_impl(ctx, bases, n_bases, read_off, read_len, n_reads, pairs, n_pairs, false, pen,
                      scores_out, cigars_out, cigar_off, cigar_len_out);
@@ -933,5 +941,5 @@ extern "C" int otgpu_edit_cigars(otgpu_ctx* ctx, const uint8_t* bases, uint64_t 
                                  int32_t* scores_out, char* cigars_out, const uint64_t* cigar_off,
                                  int32_t* cigar_len_out) {
   return cigars_impl(ctx, bases, n_bases, read_off, read_len, n_reads, pairs, n_pairs, true,
-                     AffPen{1, 0, 1, 2}, scores_out, cigars_out, cigar_off, cigar_len_out);
+                     AffPen{1, 0, 1, 2, 1}, scores_out, cigars_out, cigar_off, cigar_len_out);
 }

@@ -39,7 +39,7 @@ struct AffWork {        // per-warp workspace in HBM
   uint32_t ops_cap;
 };
 
-struct AffPen { int x, o, e, scope; };
+struct AffPen { int x, o, e, scope, step; };  // step = gcd(x, o+e, e)
 
 __device__ __forceinline__ bool in_bounds(int off, int k, int plen, int tlen) {
   return (unsigned)off <= (unsigned)tlen && (unsigned)(off - k) <= (unsigned)plen;
@@ -64,7 +64,10 @@ __device__ int wfa_affine_pair(const AffWork& W, AffSlot* __restrict__ meta, con
   const size_t rstride = (size_t)mask + 1;
   int2* const steps = reinterpret_cast<int2*>(W.slab);  // {lo, cell base} per score
   uint32_t cells_top = W.slab_bytes;                    // cells grow downward from here
-  int score = 0, null_steps = 0, end_k = 0, end_off = 0;
+  int score = 0, sm = 0, null_steps = 0, end_k = 0, end_off = 0;  // sm = score % scope
+  // every reachable score is a multiple of g = gcd(x, o+e, e): the scores in between are null
+  // steps (wavefront_compute_affine.c:199-206) and are only counted, g at a time
+  const int g = pen.step;
 
 #define RING(c, slot) (W.rings + ((size_t)(c)*scope + (slot)) * rstride)
   // ---- wavefront 0 (wavefront_align.c:113-135 / :190-245) ----
@@ -87,7 +90,6 @@ __device__ int wfa_affine_pair(const AffWork& W, AffSlot* __restrict__ meta, con
   }
 
   for (;;) {
-    const int sm = score % scope;
     const int fl = meta[sm].flags;
     // ---- extend + termination + cut-off (wavefront_extend.c:355-452) ----
     if (!(fl & 1)) {
@@ -155,24 +157,34 @@ __device__ int wfa_affine_pair(const AffWork& W, AffSlot* __restrict__ meta, con
     }
 
     // ---- compute score+1 (wavefront_compute_affine.c:192-248) ----
-    ++score;
+    if (g > 1) {  // the g-1 null scores in between (checked at their extend, :369-372)
+      null_steps += g - 1;
+      if (null_steps > scope) return -1;
+    }
+    score += g;
+    sm += g;
+    if (sm >= scope) sm -= scope;
     {
-      const int so = score % scope;
+      const int so = sm;
       if ((uint32_t)(score + 1) * 8u + 64u > cells_top) return kAffOverflow;
       const int s_mis = score - pen.x, s_open = score - pen.o - pen.e, s_ext = score - pen.e;
+      // ring slots of the three source scores (each penalty < scope)
+      const int q_mis = so - pen.x + (so < pen.x ? scope : 0);
+      const int q_open = so - pen.o - pen.e + (so < pen.o + pen.e ? scope : 0);
+      const int q_ext = so - pen.e + (so < pen.e ? scope : 0);
       // usable input = exists and not ->null (wavefront_compute.c:88-95); else lo=1, hi=-1
       int mm_lo = 1, mm_hi = -1, mo_lo = 1, mo_hi = -1, ie_lo = 1, ie_hi = -1, de_lo = 1, de_hi = -1;
       bool has_mm = false, has_mo = false, has_ie = false, has_de = false;
       if (s_mis >= 0) {
-        const AffSlot& a = meta[s_mis % scope];
+        const AffSlot& a = meta[q_mis];
         if ((a.flags & 1) && !(a.flags & 8)) { has_mm = true; mm_lo = a.lo[0]; mm_hi = a.hi[0]; }
       }
       if (s_open >= 0) {
-        const AffSlot& a = meta[s_open % scope];
+        const AffSlot& a = meta[q_open];
         if ((a.flags & 1) && !(a.flags & 8)) { has_mo = true; mo_lo = a.lo[0]; mo_hi = a.hi[0]; }
       }
       if (s_ext >= 0) {
-        const AffSlot& a = meta[s_ext % scope];
+        const AffSlot& a = meta[q_ext];
         if ((a.flags & 2) && !(a.flags & 16)) { has_ie = true; ie_lo = a.lo[1]; ie_hi = a.hi[1]; }
         if ((a.flags & 4) && !(a.flags & 32)) { has_de = true; de_lo = a.lo[2]; de_hi = a.hi[2]; }
       }
@@ -195,10 +207,10 @@ __device__ int wfa_affine_pair(const AffWork& W, AffSlot* __restrict__ meta, con
       if ((uint32_t)(score + 1) * 8u + 64u + (uint32_t)width > cells_top) return kAffOverflow;
       cells_top -= (uint32_t)width;
       const bool has_i = has_mo || has_ie, has_d = has_mo || has_de;  // wavefront_compute.c:262-283
-      const int32_t* r_mm = RING(0, s_mis >= 0 ? s_mis % scope : 0);
-      const int32_t* r_mo = RING(0, s_open >= 0 ? s_open % scope : 0);
-      const int32_t* r_ie = RING(1, s_ext >= 0 ? s_ext % scope : 0);
-      const int32_t* r_de = RING(2, s_ext >= 0 ? s_ext % scope : 0);
+      const int32_t* r_mm = RING(0, q_mis);
+      const int32_t* r_mo = RING(0, q_open);
+      const int32_t* r_ie = RING(1, q_ext);
+      const int32_t* r_de = RING(2, q_ext);
       int32_t* o_m = RING(0, so);
       int32_t* o_i = RING(1, so);
       int32_t* o_d = RING(2, so);
