@@ -177,6 +177,57 @@ def cpu_reference(B, budget_s, threads=None):
                        f"static contiguous region blocks over {threads} threads"), run, R
 
 
+def work_counts(B, n_regions=2):
+    """Algorithmic operations per pair (secondary): offset updates W and 32-base
+    word comparisons E, counted by the instrumented C restatement (oracle/wfa_oracle.c) over the
+    first regions of the workload.  Part of the cpu_baseline leg (the oracle is never on the
+    measured path)."""
+    import ctypes as C
+    port_so = os.path.join(ROOT, "oracle", "libwfa_oracle.so")
+    if not os.path.exists(port_so):
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "port"])
+    lib = C.CDLL(port_so)
+
+    class Counters(C.Structure):
+        _fields_ = [("steps", C.c_int64), ("width_sum", C.c_int64), ("extend_bases", C.c_int64),
+                    ("extend_words", C.c_int64), ("max_width", C.c_int32), ("cutoffs", C.c_int32),
+                    ("prunes", C.c_int32), ("pad_", C.c_int32), ("width_hist", C.c_int64 * 8)]
+    lib.wfo_edit_score.restype = C.c_int
+    lib.wfo_edit_score.argtypes = [C.c_char_p, C.c_int, C.c_char_p, C.c_int] + [C.c_int] * 5 + [C.c_void_p]
+    rs, off, lens = B["region_start"], B["off"], B["lens"]
+    raw = B["bases"].tobytes() if B["bases"].size < (1 << 28) else None
+    tot = dict(pairs=0, steps=0, W=0, E=0, max_width=0)
+    hist = [0] * 8
+    for g in range(min(n_regions, len(rs) - 1)):
+        reads = []
+        for r in range(int(rs[g]), int(rs[g + 1])):
+            o, n = int(off[r]), int(lens[r])
+            reads.append(raw[o:o + n] if raw is not None else B["bases"][o:o + n].tobytes())
+        for i in range(len(reads)):
+            for j in range(i + 1, len(reads)):
+                x, y = reads[i], reads[j]
+                if x == y:
+                    tot["pairs"] += 1
+                    continue
+                if len(x) < len(y):  # pattern = the longer read, tie -> x (analignments.cpp:67-70)
+                    x, y = y, x
+                c = Counters()
+                lib.wfo_edit_score(x, len(x), y, len(y), 0, 0, 0, 0, 0, C.byref(c))
+                tot["pairs"] += 1
+                tot["steps"] += c.steps
+                tot["W"] += c.width_sum
+                tot["E"] += c.extend_words
+                tot["max_width"] = max(tot["max_width"], c.max_width)
+                for b in range(8):
+                    hist[b] += c.width_hist[b]
+    n = max(tot["pairs"], 1)
+    return {"sample": f"first {min(n_regions, len(rs) - 1)} regions ({tot['pairs']} pairs), instrumented C restatement",
+            "score_steps_per_pair": tot["steps"] / n, "offset_updates_per_pair": tot["W"] / n,
+            "word_compares_per_pair": tot["E"] / n, "max_width": tot["max_width"],
+            "steps_by_width": dict(zip(("le30", "le61", "le125", "le189", "le253", "le509", "le1021",
+                                        "wider"), hist))}
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
@@ -515,6 +566,10 @@ def main():
             base, _, _ = cpu_reference(B, 15.0)
             base.pop("pairs"), base.pop("seconds")
             line["cpu_baseline"] = base
+            w = work_counts(B)
+            w["offset_updates_per_s"] = w["offset_updates_per_pair"] * value
+            w["word_compares_per_s"] = w["word_compares_per_pair"] * value
+            line["work"] = w
         print(json.dumps(line), flush=True)
     ctx.close()
     if world > 1:

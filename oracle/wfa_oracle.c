@@ -49,6 +49,12 @@ int wfo_edit_score(const char* pattern, int plen, const char* text, int tlen, in
     if (ctr) {
       ctr->width_sum += hi - lo + 1;
       if (hi - lo + 1 > ctr->max_width) ctr->max_width = hi - lo + 1;
+      {
+        static const int edge[7] = {30, 61, 125, 189, 253, 509, 1021};
+        int b = 0;
+        while (b < 7 && hi - lo + 1 > edge[b]) ++b;
+        ctr->width_hist[b]++;
+      }
     }
     for (k = lo; k <= hi; ++k) {
       int h = M[k], v, n = 0;

@@ -29,6 +29,9 @@ typedef struct {
   int32_t max_width;    /* widest wavefront seen at extend time                        */
   int32_t cutoffs;      /* steps on which the adaptive cut-off shrank the wavefront    */
   int32_t prunes;       /* exact-prune triggers (width >= 1000)                        */
+  int32_t pad_;
+  int64_t width_hist[8]; /* score steps by live width: <=30, <=61, <=125, <=189, <=253, <=509,
+                            <=1021, wider (the kernel's narrow / mid / 2, 3, 4, 8, 16 rounds)   */
 } wfo_counters;
 
 /* Edit-distance score under WF-adaptive(10,50,1).  endsfree=0: alignEnd2End(pattern,text);
