@@ -191,13 +191,15 @@ def work_counts(B, n_regions=2):
     class Counters(C.Structure):
         _fields_ = [("steps", C.c_int64), ("width_sum", C.c_int64), ("extend_bases", C.c_int64),
                     ("extend_words", C.c_int64), ("max_width", C.c_int32), ("cutoffs", C.c_int32),
-                    ("prunes", C.c_int32), ("pad_", C.c_int32), ("width_hist", C.c_int64 * 8)]
+                    ("prunes", C.c_int32), ("pad_", C.c_int32), ("width_hist", C.c_int64 * 8),
+                ("run_hist", C.c_int64 * 8)]
     lib.wfo_edit_score.restype = C.c_int
     lib.wfo_edit_score.argtypes = [C.c_char_p, C.c_int, C.c_char_p, C.c_int] + [C.c_int] * 5 + [C.c_void_p]
     rs, off, lens = B["region_start"], B["off"], B["lens"]
     raw = B["bases"].tobytes() if B["bases"].size < (1 << 28) else None
     tot = dict(pairs=0, steps=0, W=0, E=0, max_width=0)
     hist = [0] * 8
+    runs = [0] * 8
     for g in range(min(n_regions, len(rs) - 1)):
         reads = []
         for r in range(int(rs[g]), int(rs[g + 1])):
@@ -220,12 +222,15 @@ def work_counts(B, n_regions=2):
                 tot["max_width"] = max(tot["max_width"], c.max_width)
                 for b in range(8):
                     hist[b] += c.width_hist[b]
+                    runs[b] += c.run_hist[b]
     n = max(tot["pairs"], 1)
     return {"sample": f"first {min(n_regions, len(rs) - 1)} regions ({tot['pairs']} pairs), instrumented C restatement",
             "score_steps_per_pair": tot["steps"] / n, "offset_updates_per_pair": tot["W"] / n,
             "word_compares_per_pair": tot["E"] / n, "max_width": tot["max_width"],
             "steps_by_width": dict(zip(("le30", "le61", "le125", "le189", "le253", "le509", "le1021",
-                                        "wider"), hist))}
+                                        "wider"), hist)),
+            "extensions_by_matched_bases": dict(zip(("lt31", "lt62", "lt93", "lt124", "lt248", "lt1116",
+                                                     "lt4000", "more"), runs))}
 
 
 def run_reference(args, rank, world):
@@ -404,6 +409,76 @@ def run_compare(args, rank, world, local_rank):
 
 
 # ------------------------------------------------------------------------------------------------
+def run_pipeline(args, rank, world, local_rank):
+    """Integration measurement: assemble_process's loop body (src/assemble.cpp:103-142: distance
+    matrix -> otter_hclust -> re-assignment -> rapid_consensus) over a wave of regions, host reads
+    in, alleles out.  `ours` = the unmodified reference clustering / partial-order-consensus
+    objects linked on the product's host layer (oracle/_ref/libotter_intree.so, built by
+    oracle/Makefile from /root/reference + otter_b200/host): every alignment runs batched on the
+    GPU, everything else on the host threads.  `reference` = the unmodified reference
+    (libotter_ref.so), one region at a time per host thread.  Both return per-region labels and
+    allele digests; the ours arm checks them against the reference on a sample."""
+    import ctypes as C
+    if rank != 0:
+        return
+    B = workload_arrays(args.workload, 0, args.regions or 200)
+    n_regions = B["n_regions"]
+    threads = os.cpu_count() or 1
+    vp = C.c_void_p
+
+    def bind(name):
+        lib = C.CDLL(os.path.join(ROOT, "oracle", "_ref", name))
+        lib.ref_assemble_regions.restype = C.c_double
+        lib.ref_assemble_regions.argtypes = [vp, vp, vp, vp, vp, C.c_uint32, C.c_int, C.c_int, vp, vp, vp]
+        return lib
+
+    def run(lib, R):
+        labels = np.zeros(int(B["region_start"][R]), dtype=np.int32)
+        n_al = np.zeros(R, dtype=np.int32)
+        dig = np.zeros(R, dtype=np.uint64)
+        p = lambda a: a.ctypes.data_as(vp)  # noqa: E731
+        t = lib.ref_assemble_regions(p(B["bases"]), p(B["off"]), p(B["lens"]), None, p(B["region_start"]),
+                                     R, 2, threads, p(labels), p(n_al), p(dig))
+        return t, labels, n_al, dig
+
+    line = {"metric": "regions assembled/sec", "unit": "regions/s", "n_gpus": 1, "steps": args.steps,
+            "warmup": args.warmup, "higher_is_better": True, "dtype": "int32", "data": "synthetic",
+            "config": {"workload": f"{args.workload}: distance matrix + clustering + re-assignment + "
+                                   f"consensus per region, max_alleles 2", "regions": n_regions,
+                       "host_threads": threads}}
+    if args.impl == "reference":
+        lib = bind("libotter_ref.so")
+        R = min(n_regions, max(threads * 2, 32))
+        t = sum(run(lib, R)[0] for _ in range(args.steps))
+        line.update(impl="reference", value=R * args.steps / t, ms_per_step=1e3 * t / args.steps,
+                    cpu_baseline={"kind": "reference", "cores": threads, "value": R * args.steps / t,
+                                  "unit": "regions/s", "sample": f"first {R} of {n_regions} regions"})
+        print(json.dumps(line), flush=True)
+        return
+    lib = bind("libotter_intree.so")
+    for _ in range(max(args.warmup, 1)):
+        run(lib, n_regions)
+    t, res = 0.0, None
+    for _ in range(args.steps):
+        r = run(lib, n_regions)
+        t += r[0]
+        res = r[1:]
+    line.update(value=n_regions * args.steps / t, ms_per_step=1e3 * t / args.steps,
+                e2e={"value": n_regions * args.steps / t, "unit": "regions/s",
+                     "h2d_bytes_per_step": int(B["bases"].nbytes), "d2h_bytes_per_step": None},
+                note="host reads -> alleles; GPU: all alignments (batched); host threads: clustering, "
+                     "partial-order consensus (the reference's own code)")
+    if not args.no_cpu_baseline:
+        R = min(n_regions, max(threads * 2, 32))
+        tr, labels, n_al, dig = run(bind("libotter_ref.so"), R)
+        same = bool(np.array_equal(labels, res[0][:len(labels)]) and np.array_equal(n_al, res[1][:R])
+                    and np.array_equal(dig, res[2][:R]))
+        line["cpu_baseline"] = {"kind": "reference", "cores": threads, "value": R / tr, "unit": "regions/s",
+                                "sample": f"first {R} of {n_regions} regions in {tr:.2f} s"}
+        line["identical_to_reference"] = same
+    print(json.dumps(line), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -413,7 +488,7 @@ def main():
     ap.add_argument("--regions", type=int, default=None, help="override regions per GPU")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--path", default="distmatrix", choices=["distmatrix", "consensus", "compare"],
+    ap.add_argument("--path", default="distmatrix", choices=["distmatrix", "consensus", "compare", "pipeline"],
                     help="distmatrix = fill_dist_matrix (the headline); consensus = the gap-affine "
                          "+ CIGAR alignments rapid_consensus issues (secondary row)")
     args = ap.parse_args()
@@ -426,6 +501,8 @@ def main():
     if args.path == "consensus":
         run_consensus(args, rank, world, local_rank)
         return
+    if args.path == "pipeline":
+        return run_pipeline(args, rank, world, local_rank)
     if args.path == "compare":
         run_compare(args, rank, world, local_rank)
         return

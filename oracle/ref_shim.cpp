@@ -32,6 +32,7 @@
 #include <chrono>
 #include <cstdint>
 #include <cstring>
+#include <memory>
 #include <string>
 #include <thread>
 #include <vector>
@@ -232,6 +233,26 @@ int ref_ppoa_consensus(const char* bases, const uint64_t* off, const uint32_t* l
   return (int)consensus.size();
 }
 
+// The reference PPOA (src/anppoa.hpp) from given CIGARs: reads 1..n-1 inserted into the graph of
+// read 0 along cigars[coff[i], coff[i+1]), then adjust_weights(c, t) and consensus.
+int ref_ppoa_cigars(const char* bases, const uint64_t* off, const uint32_t* len, const uint8_t* span,
+                    uint32_t n, const char* cigars, const uint64_t* coff, float c, float t, char* out,
+                    int cap) {
+  PPOA poa;
+  std::string backbone(bases + off[0], len[0]);
+  poa.init(backbone);
+  for (uint32_t i = 1; i < n; ++i) {
+    std::string seq(bases + off[i], len[i]), cigar(cigars + coff[i], coff[i + 1] - coff[i]);
+    bool sl = span ? (span[i] & 1) != 0 : true, sr = span ? (span[i] & 2) != 0 : true;
+    poa.insert_alignment(seq, cigar, sl, sr);
+  }
+  poa.adjust_weights(c, t);
+  std::string consensus;
+  poa.consensus(consensus);
+  if (out && cap > 0) std::memcpy(out, consensus.data(), (int)consensus.size() < cap ? consensus.size() : cap);
+  return (int)consensus.size();
+}
+
 // local_realignment (src/analignments.cpp:11-60) against an indexed FASTA on disk.
 // ccoords = pairs (first, second) per read.  Outputs: new sequences concatenated in out_bases
 // (lengths in out_len) and new span bits.  Returns total bytes needed.
@@ -298,6 +319,141 @@ int ref_assemble_region(const char* bases, const uint64_t* off, const uint32_t* 
   *out_ic = clust.ic;
   for (uint32_t i = 0; i < n_reads; ++i) out_labels[i] = labels[i];
   return clust.fc;
+}
+
+// ---- many regions through the body of assemble_process, timed --------------------------------
+extern "C++" {
+namespace {
+template <class F>
+void parallel_blocks(uint32_t n, int threads, F&& f) {  // static contiguous blocks, as parallelize_loop
+  if (threads < 1) threads = 1;
+  std::vector<std::thread> pool;
+  const uint32_t per = (n + threads - 1) / threads;
+  for (int t = 0; t < threads; ++t) {
+    const uint32_t a = (uint32_t)t * per, b = a + per < n ? a + per : n;
+    if (a >= b) break;
+    pool.emplace_back([a, b, &f] { for (uint32_t g = a; g < b; ++g) f(g); });
+  }
+  for (auto& th : pool) th.join();
+}
+
+uint64_t fnv(uint64_t h, const void* p, size_t n) {
+  const unsigned char* c = static_cast<const unsigned char*>(p);
+  for (size_t i = 0; i < n; ++i) { h ^= c[i]; h *= 1099511628211ull; }
+  return h;
+}
+uint64_t allele_digest(const std::vector<ANALLELE>& alleles, int ic) {
+  uint64_t h = 1469598103934665603ull;
+  h = fnv(h, &ic, sizeof ic);
+  for (const auto& a : alleles) {
+    h = fnv(h, a.seq.data(), a.seq.size());
+    const int cov[3] = {a.acov, a.scov, a.tcov};
+    h = fnv(h, cov, sizeof cov);
+    const float se = a.se;
+    h = fnv(h, &se, sizeof se);
+  }
+  return h;
+}
+
+struct RegionWork {
+  std::vector<ANREAD> reads;
+  std::vector<int> valid, invalid, labels;
+  std::unique_ptr<DistMatrix> dm;
+  ClusteringStatus clust;
+  std::vector<ANALLELE> alleles;
+};
+}  // namespace
+}  // extern "C++"
+
+// assemble_process's loop body (src/assemble.cpp:103-142, defaults of command_assemble.cpp:34-45,
+// no --haps) over n_regions regions on `threads` host threads.  Per region: the labels of its
+// reads (out_labels, indexed like the reads), the number of alleles and a digest of the alleles
+// (sequence, coverages, se) + initial cluster count.  Returns wall seconds.
+//   reference build: one region at a time per thread, static contiguous blocks (parallelize_loop);
+//   in-tree build  : the same stages in one wave — every region's distance matrix in ONE batch on
+//                    the GPU, clustering per region on the host threads, re-assignment and the
+//                    consensus alignments batched on the GPU, partial-order consensus per region
+//                    on the host threads (the seam INTEGRATION.md describes).
+double ref_assemble_regions(const char* bases, const uint64_t* off, const uint32_t* len,
+                            const uint8_t* span, const uint32_t* region_start, uint32_t n_regions,
+                            int max_alleles, int threads, int32_t* out_labels,
+                            int32_t* out_n_alleles, uint64_t* out_digest) {
+  bool ignore_haps = true;
+  std::vector<RegionWork> W(n_regions);
+  const auto t0 = std::chrono::steady_clock::now();
+  auto prepare = [&](uint32_t g) {
+    RegionWork& w = W[g];
+    build_reads(bases, off, len, span, region_start[g], region_start[g + 1], w.reads);
+    for (int i = 0; i < (int)w.reads.size(); ++i)  // partition_valid_reads, src/assemble.cpp:27-37
+      (w.reads[i].is_spanning() ? w.valid : w.invalid).emplace_back(i);
+    w.labels.assign(w.reads.size(), -1);
+    if (!w.valid.empty()) w.dm.reset(new DistMatrix(w.valid.size()));
+  };
+  auto cluster = [&](uint32_t g, wfa::WFAligner& unused) {
+    RegionWork& w = W[g];
+    if (w.valid.empty()) return;
+    otter_hclust(ignore_haps, max_alleles, 0.01, 500, 0.015, 0.01, 0.2, 500, 0.1, w.valid, *w.dm,
+                 unused, w.reads, w.clust);
+    for (uint32_t i = 0; i < w.clust.labels.size(); ++i) w.labels[w.valid[i]] = w.clust.labels[i];
+    w.alleles.resize(w.clust.fc);
+  };
+  auto publish = [&](uint32_t g) {
+    RegionWork& w = W[g];
+    for (uint32_t i = 0; i < w.labels.size(); ++i) out_labels[region_start[g] + i] = w.labels[i];
+    out_n_alleles[g] = w.valid.empty() ? 0 : w.clust.fc;
+    out_digest[g] = w.valid.empty() ? 0 : allele_digest(w.alleles, w.clust.ic);
+  };
+#ifndef OTTER_B200_IN_TREE
+  parallel_blocks(n_regions, threads, [&](uint32_t g) {
+    prepare(g);
+    RegionWork& w = W[g];
+    if (!w.valid.empty()) {
+      auto& A = tls();
+      if (max_alleles != 1) fill_dist_matrix(ignore_haps, A.edit, w.reads, w.valid, *w.dm);
+      cluster(g, A.edit);
+      if (!w.invalid.empty())
+        invalid_reassignment(ignore_haps, 0.9, 0.01, w.clust.fc, w.reads, A.edit, w.labels);
+      rapid_consensus(ignore_haps, w.reads, w.labels, w.valid, w.clust.fc, *w.dm, A.affine, w.alleles);
+    }
+    publish(g);
+  });
+#else
+  auto& A = tls();
+  parallel_blocks(n_regions, threads, prepare);
+  if (max_alleles != 1) {
+    std::vector<RegionDistJob> jobs;
+    for (auto& w : W)
+      if (!w.valid.empty()) jobs.push_back({&w.reads, &w.valid, w.dm.get()});
+    fill_dist_matrices(ignore_haps, A.edit, jobs);
+  }
+  parallel_blocks(n_regions, threads, [&](uint32_t g) { cluster(g, A.edit); });
+  {
+    std::vector<RegionReassignJob> jobs;
+    for (auto& w : W)
+      if (!w.valid.empty() && !w.invalid.empty()) jobs.push_back({&w.reads, &w.labels, w.clust.fc});
+    if (!jobs.empty()) invalid_reassignments(ignore_haps, 0.9, 0.01, A.edit, jobs);
+  }
+  std::vector<ConsensusJob> cjobs;
+  std::vector<uint32_t> cjob_of(n_regions, UINT32_MAX);
+  for (uint32_t g = 0; g < n_regions; ++g) {
+    RegionWork& w = W[g];
+    if (w.valid.empty()) continue;
+    cjob_of[g] = (uint32_t)cjobs.size();
+    cjobs.emplace_back();
+    ConsensusJob& j = cjobs.back();
+    j.reads = &w.reads;
+    j.labels = &w.labels;
+    j.valid_indeces = &w.valid;
+    j.total_alleles = w.clust.fc;
+    j.valid_distmatrix = w.dm.get();
+  }
+  rapid_consensus_alignments(A.affine, cjobs);
+  parallel_blocks(n_regions, threads, [&](uint32_t g) {
+    if (cjob_of[g] != UINT32_MAX) rapid_consensus_finish(ignore_haps, cjobs[cjob_of[g]], W[g].alleles);
+    publish(g);
+  });
+#endif
+  return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
 
 // aligner2 over a list of (pattern, text, pb, pe, tb, te) requests (pb < 0: end-to-end), static

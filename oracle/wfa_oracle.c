@@ -65,6 +65,12 @@ int wfo_edit_score(const char* pattern, int plen, const char* text, int tlen, in
       if (ctr) {
         ctr->extend_bases += n;
         ctr->extend_words += n / 32 + 1;
+        {
+          static const int edge[7] = {31, 62, 93, 124, 248, 1116, 4000};
+          int b = 0;
+          while (b < 7 && n >= edge[b]) ++b;
+          ctr->run_hist[b]++;
+        }
       }
       if (endsfree) { /* wavefront_extend.c:122-168, tested per k in ascending order */
         const int hh = h + n, vv = hh - k;

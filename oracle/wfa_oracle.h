@@ -32,6 +32,7 @@ typedef struct {
   int32_t pad_;
   int64_t width_hist[8]; /* score steps by live width: <=30, <=61, <=125, <=189, <=253, <=509,
                             <=1021, wider (the kernel's narrow / mid / 2, 3, 4, 8, 16 rounds)   */
+  int64_t run_hist[8];   /* extensions by matched bases: <31, <62, <93, <124, <248, <1116, <4000, more */
 } wfo_counters;
 
 /* Edit-distance score under WF-adaptive(10,50,1).  endsfree=0: alignEnd2End(pattern,text);

@@ -94,14 +94,22 @@ struct ConsensusJob {
 };
 void rapid_consensus_alignments(wfa::WFAligner& aligner2, std::vector<ConsensusJob>& jobs);
 
-#ifdef OTTER_B200_IN_TREE
-#include "anfahelper.hpp"
-// Reference signatures; the alignment calls inside run batched on the GPU.
-void local_realignment(const std::string& chr, const int& start, const int& end, const int& flank,
-                       const double& min_sim, const FaidxInstance& faidx_inst,
-                       std::vector<ANREAD>& reads, wfa::WFAligner& aligner);
+// rapid_consensus with the reference signature (src/analignments.hpp:62-71): alignments batched
+// on the GPU, allele bookkeeping as the reference, partial-order consensus by ppoa_b200.hpp.
 void rapid_consensus(const bool& ignore_haps, std::vector<ANREAD>& reads, std::vector<int>& labels,
                      std::vector<int>& valid_indeces, int& total_alleles,
                      DistMatrix& valid_distmatrix, wfa::WFAligner& aligner,
                      std::vector<ANALLELE>& alleles);
+// Its host half (src/analignments.cpp:227-298: coverage, standard error, haplotag check,
+// partial-order consensus) for one job whose plans rapid_consensus_alignments has filled — lets a
+// caller batch the alignments of many regions and finish each region on its own host thread.
+void rapid_consensus_finish(const bool& ignore_haps, ConsensusJob& job,
+                            std::vector<ANALLELE>& alleles);
+
+#ifdef OTTER_B200_IN_TREE
+#include "anfahelper.hpp"
+// Reference signature; the alignment calls inside run batched on the GPU.
+void local_realignment(const std::string& chr, const int& start, const int& end, const int& flank,
+                       const double& min_sim, const FaidxInstance& faidx_inst,
+                       std::vector<ANREAD>& reads, wfa::WFAligner& aligner);
 #endif

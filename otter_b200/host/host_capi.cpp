@@ -7,6 +7,7 @@
 
 #include "analignments_b200.hpp"
 #include "compare_b200.hpp"
+#include "ppoa_b200.hpp"
 
 namespace {
 std::vector<ANREAD> build_reads(const char* bases, const uint64_t* off, const uint32_t* len,
@@ -148,5 +149,25 @@ void othost_get_distances(const char* bases, const uint64_t* off, const uint32_t
   for (size_t r = 0; r < d.size(); ++r) {
     out[4 * r] = d[r].i; out[4 * r + 1] = d[r].j; out[4 * r + 2] = d[r].edit; out[4 * r + 3] = d[r].ops;
   }
+}
+
+// Partial-order consensus (ppoa_b200.hpp; reference src/anppoa.hpp) from given CIGARs: reads
+// 1..n-1 threaded through the graph of read 0 (the backbone) along cigars[i] (CIGAR i occupies
+// cigars[coff[i], coff[i+1]); entry 0 is unused), span bits as elsewhere, then
+// adjust_weights(c, t) and consensus.  No device involved.  Returns the consensus length.
+int othost_ppoa_cigars(const char* bases, const uint64_t* off, const uint32_t* len,
+                       const uint8_t* span, uint32_t n, const char* cigars, const uint64_t* coff,
+                       float c, float t, char* out, int cap) {
+  otb200::Ppoa poa;
+  poa.init(std::string(bases + off[0], len[0]));
+  for (uint32_t i = 1; i < n; ++i)
+    poa.insert_alignment(std::string(bases + off[i], len[i]),
+                         std::string(cigars + coff[i], coff[i + 1] - coff[i]),
+                         span ? (span[i] & 1) != 0 : true, span ? (span[i] & 2) != 0 : true);
+  poa.adjust_weights(c, t);
+  std::string consensus;
+  poa.consensus(consensus);
+  if (out && cap > 0) std::memcpy(out, consensus.data(), (int)consensus.size() < cap ? consensus.size() : cap);
+  return (int)consensus.size();
 }
 }

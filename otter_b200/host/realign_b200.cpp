@@ -9,8 +9,11 @@
 #include <iostream>
 #include <map>
 
+#include <cmath>
+
 #include "analignments_b200.hpp"
 #include "otter_b200.h"
+#include "ppoa_b200.hpp"
 
 namespace {
 
@@ -235,13 +238,8 @@ void rapid_consensus_alignments(wfa::WFAligner& aligner2, std::vector<ConsensusJ
 
 #ifdef OTTER_B200_IN_TREE
 // -------------------------------------------------------------------------------------------------
-// Reference signatures (src/analignments.hpp:26-35,62-71) for an in-tree build: everything that
-// is not an alignment (flank fetch, allele bookkeeping, partial-order consensus) is otter's own
-// code, called in the reference's order.
-#include <cmath>
-
-#include "anppoa.hpp"
-
+// Reference signature (src/analignments.hpp:26-35) for an in-tree build: the flank fetch is
+// otter's own code (FaidxInstance), the alignments run batched on the GPU.
 void local_realignment(const std::string& chr, const int& start, const int& end, const int& flank,
                        const double& min_sim, const FaidxInstance& faidx_inst,
                        std::vector<ANREAD>& reads, wfa::WFAligner& aligner) {
@@ -259,7 +257,12 @@ void local_realignment(const std::string& chr, const int& start, const int& end,
   std::vector<RealignJob> one{{flank, min_sim, &ref_left, &ref_right, &reads}};
   local_realignments(aligner, one);
 }
+#endif  // OTTER_B200_IN_TREE
 
+// -------------------------------------------------------------------------------------------------
+// rapid_consensus (reference src/analignments.cpp:192-298, signature src/analignments.hpp:62-71):
+// the alignments run batched on the GPU, the allele bookkeeping follows the reference line by
+// line, the partial-order consensus is ppoa_b200.hpp (same result as otter's PPOA, linear time).
 namespace {
 double standard_error(const std::vector<double>& values) {  // compute_se, :179-190
   if (values.empty()) return -1.0;
@@ -282,8 +285,16 @@ void rapid_consensus(const bool& ignore_haps, std::vector<ANREAD>& reads, std::v
   one[0].total_alleles = total_alleles;
   one[0].valid_distmatrix = &valid_distmatrix;
   rapid_consensus_alignments(aligner, one);
+  rapid_consensus_finish(ignore_haps, one[0], alleles);
+}
+
+void rapid_consensus_finish(const bool& ignore_haps, ConsensusJob& job,
+                            std::vector<ANALLELE>& alleles) {
+  std::vector<ANREAD>& reads = *job.reads;
+  DistMatrix& valid_distmatrix = *job.valid_distmatrix;
+  const int total_alleles = job.total_alleles;
   for (int label = 0; label < total_alleles; ++label) {
-    const ConsensusPlan& P = one[0].plans[label];
+    const ConsensusPlan& P = job.plans[label];
     auto& allele = alleles[label];
     allele.tcov = reads.size();               // :227-229
     allele.acov = P.members.size() + 1;
@@ -318,7 +329,7 @@ void rapid_consensus(const bool& ignore_haps, std::vector<ANREAD>& reads, std::v
       allele.seq = reads[P.valid_reads.front()].seq;
       continue;
     }
-    PPOA poa;  // otter's partial-order consensus, unchanged (src/anppoa.hpp)
+    otb200::Ppoa poa;  // src/anppoa.hpp restated (ppoa_b200.hpp)
     poa.init(reads[P.rep].seq);
     for (size_t m = 0; m < P.members.size(); ++m) {
       ANREAD& read = reads[P.members[m]];
@@ -333,4 +344,3 @@ void rapid_consensus(const bool& ignore_haps, std::vector<ANREAD>& reads, std::v
     if (allele.seq.empty()) allele.seq = "N";
   }
 }
-#endif  // OTTER_B200_IN_TREE

@@ -25,7 +25,8 @@ vp = C.c_void_p
 class Counters(C.Structure):
     _fields_ = [("steps", C.c_int64), ("width_sum", C.c_int64), ("extend_bases", C.c_int64),
                 ("extend_words", C.c_int64), ("max_width", C.c_int32), ("cutoffs", C.c_int32),
-                ("prunes", C.c_int32), ("pad_", C.c_int32), ("width_hist", C.c_int64 * 8)]
+                ("prunes", C.c_int32), ("pad_", C.c_int32), ("width_hist", C.c_int64 * 8),
+                ("run_hist", C.c_int64 * 8)]
 
 
 _port = None
@@ -141,6 +142,24 @@ def assemble_region(lib, reads, span, max_alleles=2):
         pos += int(seq_len[a])
     return dict(n_alleles=k, labels=labels.tolist(), alleles=alleles, cov=cov[:3 * k].tolist(),
                 se=[float(x).hex() for x in se[:k]], ic=ic.value)
+
+
+def assemble_regions(lib, regions, spans, max_alleles=2, threads=4):
+    """Many regions through ref_assemble_regions (reference: per region on host threads; in-tree:
+    one wave with the alignments batched on the GPU) -> (labels per region, n_alleles, digests)."""
+    reads = [r for reg in regions for r in reg]
+    bases, off, lens = pack_reads(reads)
+    sp = np.array([x for s in spans for x in s], dtype=np.uint8)
+    rs = np.zeros(len(regions) + 1, dtype=np.uint32)
+    rs[1:] = np.cumsum([len(r) for r in regions])
+    labels = np.zeros(len(reads), dtype=np.int32)
+    n_al = np.zeros(len(regions), dtype=np.int32)
+    dig = np.zeros(len(regions), dtype=np.uint64)
+    lib.ref_assemble_regions.restype = c_dbl
+    lib.ref_assemble_regions.argtypes = [vp, vp, vp, vp, vp, c_u32, c_int, c_int, vp, vp, vp]
+    lib.ref_assemble_regions(ptr(bases), ptr(off), ptr(lens), ptr(sp), ptr(rs), len(regions), max_alleles,
+                             threads, ptr(labels), ptr(n_al), ptr(dig))
+    return [labels[rs[g]:rs[g + 1]].tolist() for g in range(len(regions))], n_al.tolist(), dig.tolist()
 
 
 from otter_b200.synth import (ALPHA, rand_seq, mutate, tr_region, pack_reads,  # noqa: E402,F401

@@ -187,3 +187,40 @@ def test_whole_regions_equal_reference_live(built):
         assert a == b, trial
         n_alleles.append(a["n_alleles"])
     assert max(n_alleles) == 2
+
+
+@pytest.mark.skipif(not (S.have_intree() and S.have_ref()), reason="needs both prebuilt pipeline libraries")
+def test_wave_of_regions_equals_reference(built):
+    """assemble_process's loop body over many regions at once: the in-tree build runs every
+    region's distance matrix, re-assignment and consensus alignments as ONE batch each on the GPU
+    (clustering and partial-order consensus on host threads); labels, allele counts and allele
+    digests must equal the reference run region by region, and region by region through the
+    single-region entry point."""
+    T, R = S.intree(), S.ref()
+    rng = np.random.default_rng(808)
+    regions, spans = [], []
+    for trial in range(24):
+        motif = S.rand_seq(rng, int(rng.integers(2, 7)))
+        fl, fr = S.rand_seq(rng, 100), S.rand_seq(rng, 100)
+        c0 = int(rng.integers(30, 160))
+        al = [np.concatenate([fl, np.tile(motif, c), fr]) for c in (c0, c0 + int(rng.integers(0, 40)))]
+        e = float(rng.choice([0.005, 0.02, 0.05]))
+        n = int(rng.integers(1, 30))
+        reads = [S.mutate(rng, al[int(rng.integers(0, 2))], e, n_rate=0.05) for _ in range(n)]
+        span = [3] * n
+        if trial % 3 == 0:  # partial reads: re-assignment + ends-free consensus alignments
+            for a in (0, 1):
+                r = S.mutate(rng, al[a], e)
+                cut = int(rng.integers(10, 80))
+                reads += [r[:-cut], r[cut:], r[cut // 2:-cut // 2]]
+                span += [1, 2, 0]
+        if trial == 5:  # a region without any spanning read
+            span = [1] * len(span)
+        regions.append(reads)
+        spans.append(span)
+    la, na, da = S.assemble_regions(R, regions, spans, threads=4)
+    lb, nb, db = S.assemble_regions(T, regions, spans, threads=4)
+    assert na == nb and la == lb and da == db
+    assert na[5] == 0 and max(na) == 2
+    one = S.assemble_region(R, regions[0], spans[0])
+    assert one["labels"] == la[0] and one["n_alleles"] == na[0]
