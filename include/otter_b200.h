@@ -155,6 +155,24 @@ int otgpu_edit_cigars(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
                       const otgpu_pair* pairs, uint64_t n_pairs, int32_t* scores_out,
                       char* cigars_out, const uint64_t* cigar_off, int32_t* cigar_len_out);
 
+/* ---- packed CIGAR output --------------------------------------------------------------------- */
+/* The same two alignments for a caller that wants the strings themselves in bulk (rapid_consensus
+ * feeding every CIGAR to the partial-order graph, src/analignments.cpp:280-282): the CIGARs are
+ * packed end to end on the device and only the bytes they occupy are copied, into pinned memory
+ * the context owns.  CIGAR i is (*cigars)[(*cigar_begin)[i] .. (*cigar_begin)[i] + cigar_len_out[i])
+ * (no terminator; failed alignments occupy nothing); (*cigar_begin)[n_pairs] is the total.  Both
+ * arrays stay valid until the next call on ctx.  scores_out / cigar_len_out as above. */
+int otgpu_affine_cigars_packed(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                               const uint64_t* read_off, const uint32_t* read_len, uint32_t n_reads,
+                               const otgpu_pair* pairs, uint64_t n_pairs, int mismatch, int gap_open,
+                               int gap_ext, int32_t* scores_out, int32_t* cigar_len_out,
+                               const char** cigars, const uint64_t** cigar_begin);
+int otgpu_edit_cigars_packed(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                             const uint64_t* read_off, const uint32_t* read_len, uint32_t n_reads,
+                             const otgpu_pair* pairs, uint64_t n_pairs, int32_t* scores_out,
+                             int32_t* cigar_len_out, const char** cigars,
+                             const uint64_t** cigar_begin);
+
 #ifdef __cplusplus
 }
 #endif

@@ -20,6 +20,7 @@
 #include "bindings/cpp/WFAligner.hpp"
 #ifdef OTTER_B200_IN_TREE
 #include "analignments_b200.hpp"
+#include "wave_b200.hpp"
 #else
 #include "analignments.hpp"
 #endif
@@ -31,8 +32,11 @@
 
 #include <chrono>
 #include <cstdint>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -418,40 +422,73 @@ double ref_assemble_regions(const char* bases, const uint64_t* off, const uint32
     publish(g);
   });
 #else
+  // one wave at a time through device / host stages, overlapped (otter_b200/host/wave_b200.hpp)
   auto& A = tls();
-  parallel_blocks(n_regions, threads, prepare);
-  if (max_alleles != 1) {
-    std::vector<RegionDistJob> jobs;
-    for (auto& w : W)
-      if (!w.valid.empty()) jobs.push_back({&w.reads, &w.valid, w.dm.get()});
-    fill_dist_matrices(ignore_haps, A.edit, jobs);
-  }
-  parallel_blocks(n_regions, threads, [&](uint32_t g) { cluster(g, A.edit); });
-  {
-    std::vector<RegionReassignJob> jobs;
-    for (auto& w : W)
-      if (!w.valid.empty() && !w.invalid.empty()) jobs.push_back({&w.reads, &w.labels, w.clust.fc});
-    if (!jobs.empty()) invalid_reassignments(ignore_haps, 0.9, 0.01, A.edit, jobs);
-  }
-  std::vector<ConsensusJob> cjobs;
-  std::vector<uint32_t> cjob_of(n_regions, UINT32_MAX);
-  for (uint32_t g = 0; g < n_regions; ++g) {
-    RegionWork& w = W[g];
-    if (w.valid.empty()) continue;
-    cjob_of[g] = (uint32_t)cjobs.size();
-    cjobs.emplace_back();
-    ConsensusJob& j = cjobs.back();
-    j.reads = &w.reads;
-    j.labels = &w.labels;
-    j.valid_indeces = &w.valid;
-    j.total_alleles = w.clust.fc;
-    j.valid_distmatrix = w.dm.get();
-  }
-  rapid_consensus_alignments(A.affine, cjobs);
-  parallel_blocks(n_regions, threads, [&](uint32_t g) {
-    if (cjob_of[g] != UINT32_MAX) rapid_consensus_finish(ignore_haps, cjobs[cjob_of[g]], W[g].alleles);
-    publish(g);
-  });
+  const bool stages = getenv("OTREF_STAGES") != nullptr;
+  std::mutex log_mu;
+  auto timed = [&](const char* what, auto&& body) {
+    const auto a0 = std::chrono::steady_clock::now();
+    body();
+    if (stages) {
+      std::lock_guard<std::mutex> lk(log_mu);
+      fprintf(stderr, "  [wave] %-28s %8.2f ms\n", what,
+              std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - a0).count());
+    }
+  };
+  auto blocks = [&](uint32_t a, uint32_t b, auto&& f) {
+    parallel_blocks(b - a, threads, [&](uint32_t i) { f(a + i); });
+  };
+  std::vector<ConsensusJob> cjobs(n_regions);  // one slot per region (unused when no valid read)
+  otb200::WaveStages st;
+  st.device1 = [&](uint32_t a, uint32_t b) {
+    timed("build reads", [&] { blocks(a, b, prepare); });
+    timed("distance matrices (GPU)", [&] {
+      if (max_alleles == 1) return;
+      std::vector<RegionDistJob> jobs;
+      for (uint32_t g = a; g < b; ++g)
+        if (!W[g].valid.empty()) jobs.push_back({&W[g].reads, &W[g].valid, W[g].dm.get()});
+      fill_dist_matrices(ignore_haps, A.edit, jobs);
+    });
+  };
+  st.host1 = [&](uint32_t a, uint32_t b) {
+    timed("otter_hclust (host)", [&] { blocks(a, b, [&](uint32_t g) { cluster(g, A.edit); }); });
+  };
+  st.device2 = [&](uint32_t a, uint32_t b) {
+    timed("re-assignment + consensus alignments (GPU)", [&] {
+      std::vector<RegionReassignJob> rjobs;
+      for (uint32_t g = a; g < b; ++g)
+        if (!W[g].valid.empty() && !W[g].invalid.empty())
+          rjobs.push_back({&W[g].reads, &W[g].labels, W[g].clust.fc});
+      if (!rjobs.empty()) invalid_reassignments(ignore_haps, 0.9, 0.01, A.edit, rjobs);
+      std::vector<ConsensusJob> batch;
+      std::vector<uint32_t> owner;
+      for (uint32_t g = a; g < b; ++g) {
+        RegionWork& w = W[g];
+        if (w.valid.empty()) continue;
+        ConsensusJob j;
+        j.reads = &w.reads;
+        j.labels = &w.labels;
+        j.valid_indeces = &w.valid;
+        j.total_alleles = w.clust.fc;
+        j.valid_distmatrix = w.dm.get();
+        batch.push_back(std::move(j));
+        owner.push_back(g);
+      }
+      rapid_consensus_alignments(A.affine, batch);
+      for (size_t i = 0; i < batch.size(); ++i) cjobs[owner[i]] = std::move(batch[i]);
+    });
+  };
+  st.host2 = [&](uint32_t a, uint32_t b) {
+    timed("partial-order consensus (host)", [&] {
+      blocks(a, b, [&](uint32_t g) {
+        if (!W[g].valid.empty()) rapid_consensus_finish(ignore_haps, cjobs[g], W[g].alleles);
+        publish(g);
+      });
+    });
+  };
+  uint32_t wave = 64;
+  if (const char* e = getenv("OTREF_WAVE")) wave = (uint32_t)atoi(e);
+  otb200::run_waves(n_regions, wave, st);
 #endif
   return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }

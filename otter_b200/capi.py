@@ -14,7 +14,8 @@ SYMBOLS = [
     "otgpu_host_free", "otgpu_edit_scores", "otgpu_region_edit_scores",
     "otgpu_batch_upload_regions", "otgpu_batch_upload_pairs", "otgpu_batch_align",
     "otgpu_batch_download", "otgpu_synchronize", "otgpu_last_align_ms", "otgpu_affine_cigars",
-    "otgpu_edit_cigars", "otgpu_last_chunk_count",
+    "otgpu_edit_cigars", "otgpu_last_chunk_count", "otgpu_affine_cigars_packed",
+    "otgpu_edit_cigars_packed",
 ]
 
 
@@ -74,6 +75,10 @@ def lib():
         l.otgpu_last_align_ms.argtypes = [vp, C.POINTER(C.c_float * 4)]
         l.otgpu_affine_cigars.argtypes = [vp, vp, u64, vp, vp, u32, vp, u64, i32, i32, i32, vp, vp, vp, vp]
         l.otgpu_edit_cigars.argtypes = [vp, vp, u64, vp, vp, u32, vp, u64, vp, vp, vp, vp]
+        l.otgpu_affine_cigars_packed.argtypes = [vp, vp, u64, vp, vp, u32, vp, u64, i32, i32, i32, vp, vp,
+                                                 C.POINTER(vp), C.POINTER(vp)]
+        l.otgpu_edit_cigars_packed.argtypes = [vp, vp, u64, vp, vp, u32, vp, u64, vp, vp,
+                                               C.POINTER(vp), C.POINTER(vp)]
         l.otgpu_last_chunk_count.restype = u64
         l.otgpu_last_chunk_count.argtypes = [vp]
         _lib = l
@@ -170,6 +175,29 @@ class Context:
         self._ck(self._l.otgpu_edit_cigars(self._h, _p(bases), bases.size, _p(off), _p(lens), len(lens),
                                            _p(pairs), n, _p(scores), None, None, _p(clen)))
         return scores, clen
+
+    def cigars_packed(self, bases, off, lens, pairs, x=4, o=6, e=2, edit=False):
+        """Packed output: -> (scores, lengths, begin uint64[n+1], packed uint8[total]); the last two
+        are views of pinned memory the context owns, valid until the next call."""
+        pairs = np.ascontiguousarray(pairs, dtype=PAIR_DTYPE)
+        n = len(pairs)
+        scores = np.zeros(n, dtype=np.int32)
+        clen = np.zeros(n, dtype=np.int32)
+        pc, pb = C.c_void_p(), C.c_void_p()
+        if edit:
+            self._ck(self._l.otgpu_edit_cigars_packed(self._h, _p(bases), bases.size, _p(off), _p(lens),
+                                                      len(lens), _p(pairs), n, _p(scores), _p(clen),
+                                                      C.byref(pc), C.byref(pb)))
+        else:
+            self._ck(self._l.otgpu_affine_cigars_packed(self._h, _p(bases), bases.size, _p(off), _p(lens),
+                                                        len(lens), _p(pairs), n, x, o, e, _p(scores),
+                                                        _p(clen), C.byref(pc), C.byref(pb)))
+        if n == 0 or not pb.value:
+            return scores, clen, np.zeros(1, np.uint64), np.zeros(0, np.uint8)
+        begin = np.ctypeslib.as_array(C.cast(pb, C.POINTER(C.c_uint64)), shape=(n + 1,))
+        total = int(begin[n])
+        packed = np.ctypeslib.as_array(C.cast(pc, C.POINTER(C.c_uint8)), shape=(max(total, 1),))[:total]
+        return scores, clen, begin, packed
 
     def affine_cigars(self, bases, off, lens, pairs, x=4, o=6, e=2, edit=False):
         """-> (scores int32[n], list of CIGAR bytes or negative status ints)."""

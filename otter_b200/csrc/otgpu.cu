@@ -230,6 +230,11 @@ struct otgpu_ctx {
   DevBuf bases, read_off, read_len, pk_off, read_flag, packed, region_start, score_off, pairs,
       scores, ovf_list, counters, wide_ws, order, order_ctl;
   DevBuf aff_rings, aff_slab, aff_slab2, aff_ops, cigar_off, cigars, cigar_len;  // gap-affine path
+  DevBuf cigar_begin, cigars_packed;            // packed CIGAR output (device side)
+  void* h_cigars = nullptr;                     // pinned: packed CIGARs of the last call
+  size_t h_cigars_cap = 0;
+  void* h_cigar_begin = nullptr;                // pinned: n_pairs + 1 start offsets
+  size_t h_cigar_begin_cap = 0;
   void* h_pk_off = nullptr;  // pinned
   size_t h_pk_off_cap = 0;
   void* h_counters = nullptr;  // pinned, 4 x u64
@@ -434,11 +439,13 @@ void otgpu_destroy(otgpu_ctx* ctx) {
                     &ctx->packed, &ctx->region_start, &ctx->score_off, &ctx->pairs, &ctx->scores,
                     &ctx->ovf_list, &ctx->counters, &ctx->wide_ws, &ctx->order, &ctx->order_ctl, &ctx->aff_rings,
                     &ctx->aff_slab, &ctx->aff_slab2, &ctx->aff_ops, &ctx->cigar_off, &ctx->cigars,
-                    &ctx->cigar_len};
+                    &ctx->cigar_len, &ctx->cigar_begin, &ctx->cigars_packed};
   for (DevBuf* b : bufs)
     if (b->p) cudaFree(b->p);
   if (ctx->h_pk_off) cudaFreeHost(ctx->h_pk_off);
   if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
+  if (ctx->h_cigars) cudaFreeHost(ctx->h_cigars);
+  if (ctx->h_cigar_begin) cudaFreeHost(ctx->h_cigar_begin);
   for (cudaEvent_t e : ctx->ev)
     if (e) cudaEventDestroy(e);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -828,21 +835,76 @@ k_affine(DevBatch b, Counters* __restrict__ ctr, uint32_t* __restrict__ ovf_list
 }  // namespace
 
 namespace {
+// Packed CIGAR output: start offsets = exclusive scan of the CIGAR lengths (failed alignments
+// count 0), one CTA; then one warp per CIGAR moves it from its capacity slot to its packed place.
+__global__ void __launch_bounds__(1024)
+k_cigar_scan(const int32_t* __restrict__ len, const uint64_t n, uint64_t* __restrict__ begin) {
+  __shared__ uint64_t part[1024];
+  const uint64_t per = (n + 1023) / 1024, a = threadIdx.x * per, b = a + per < n ? a + per : n;
+  uint64_t sum = 0;
+  for (uint64_t i = a; i < b; ++i) sum += len[i] > 0 ? (uint64_t)len[i] : 0;
+  part[threadIdx.x] = sum;
+  __syncthreads();
+  for (int d = 1; d < 1024; d <<= 1) {
+    const uint64_t v = threadIdx.x >= d ? part[threadIdx.x - d] : 0;
+    __syncthreads();
+    part[threadIdx.x] += v;
+    __syncthreads();
+  }
+  uint64_t at = part[threadIdx.x] - sum;
+  for (uint64_t i = a; i < b; ++i) {
+    begin[i] = at;
+    at += len[i] > 0 ? (uint64_t)len[i] : 0;
+  }
+  if (threadIdx.x == 1023) begin[n] = part[1023];
+}
+
+__global__ void __launch_bounds__(kCtaThreads)
+k_cigar_pack(const char* __restrict__ cigars, const uint64_t* __restrict__ cap_off,
+             const uint64_t* __restrict__ begin, const int32_t* __restrict__ len, const uint64_t n,
+             char* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const uint64_t warps = (uint64_t)gridDim.x * kWarpsPerCta;
+  for (uint64_t i = (uint64_t)blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5); i < n; i += warps) {
+    const int l = len[i];
+    const char* src = cigars + cap_off[i];
+    char* dst = out + begin[i];
+    for (int k = lane; k < l; k += 32) dst[k] = src[k];
+  }
+}
+}  // namespace
+
+namespace {
 // Alignments with CIGAR, gap-affine (edit = false) or edit distance (edit = true): same batch
 // upload, per-warp HBM workspace, two-tier trace slab and result download.
 int cigars_impl(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const uint64_t* read_off,
                 const uint32_t* read_len, uint32_t n_reads, const otgpu_pair* pairs,
                 uint64_t n_pairs, const bool edit, AffPen pen, int32_t* scores_out, char* cigars_out,
-                const uint64_t* cigar_off, int32_t* cigar_len_out) {
+                const uint64_t* cigar_off, int32_t* cigar_len_out,
+                const char** packed_out = nullptr, const uint64_t** packed_begin = nullptr) {
   if (!ctx || ((!scores_out || !cigar_len_out) && n_pairs)) return OTGPU_ERR_ARGS;
   if (!cigar_off && cigars_out) return OTGPU_ERR_ARGS;  // both null = lengths only
+  const bool packed = packed_out != nullptr;
+  if (packed && (!packed_begin || cigars_out || cigar_off)) return OTGPU_ERR_ARGS;
   int s = otgpu_batch_upload_pairs(ctx, bases, n_bases, read_off, read_len, n_reads, pairs, n_pairs);
   if (s != OTGPU_OK) return s;
+  if (packed) {
+    *packed_out = nullptr;
+    *packed_begin = nullptr;
+  }
   if (n_pairs == 0) return OTGPU_OK;
+  std::vector<uint64_t> own_off;
+  if (packed) {  // capacity slots on the device only: a CIGAR is never longer than |pattern|+|text|
+    own_off.resize(n_pairs + 1);
+    own_off[0] = 0;
+    for (uint64_t i = 0; i < n_pairs; ++i)
+      own_off[i + 1] = own_off[i] + read_len[pairs[i].pattern] + read_len[pairs[i].text];
+    cigar_off = own_off.data();
+  }
   const uint64_t cig_bytes = cigar_off ? cigar_off[n_pairs] : 0;
   for (uint64_t i = 0; cigar_off && i < n_pairs; ++i)
     if (cigar_off[i + 1] < cigar_off[i]) return OTGPU_ERR_ARGS;
-  if (cig_bytes && !cigars_out) return OTGPU_ERR_ARGS;
+  if (cig_bytes && !cigars_out && !packed) return OTGPU_ERR_ARGS;
   CK(cudaSetDevice(ctx->device));
   cudaStream_t st = ctx->stream;
   // per-warp workspace: rings cover every diagonal of the longest pair, so they never alias
@@ -908,7 +970,42 @@ int cigars_impl(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const ui
   }
   CK(cudaMemcpyAsync(scores_out, ctx->scores.p, n_pairs * 4, cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(cigar_len_out, ctx->cigar_len.p, n_pairs * 4, cudaMemcpyDeviceToHost, st));
-  if (cig_bytes) CK(cudaMemcpyAsync(cigars_out, ctx->cigars.p, cig_bytes, cudaMemcpyDeviceToHost, st));
+  if (packed) {
+    // only the bytes the CIGARs occupy leave the device, into pinned memory the context keeps
+    RS(cigar_begin, (n_pairs + 1) * 8);
+    RS(cigars_packed, cig_bytes + 16);
+    if ((n_pairs + 1) * 8 > ctx->h_cigar_begin_cap) {
+      if (ctx->h_cigar_begin) cudaFreeHost(ctx->h_cigar_begin);
+      ctx->h_cigar_begin = nullptr;
+      ctx->h_cigar_begin_cap = 0;
+      const size_t want = (n_pairs + 1) * 8 + n_pairs + 4096;
+      CK(cudaMallocHost(&ctx->h_cigar_begin, want));
+      ctx->h_cigar_begin_cap = want;
+    }
+    uint64_t* d_begin = static_cast<uint64_t*>(ctx->cigar_begin.p);
+    k_cigar_scan<<<1, 1024, 0, st>>>(static_cast<const int32_t*>(ctx->cigar_len.p), n_pairs, d_begin);
+    k_cigar_pack<<<ctx->n_sm * 8, kCtaThreads, 0, st>>>(
+        static_cast<const char*>(ctx->cigars.p), d_cigar_off, d_begin,
+        static_cast<const int32_t*>(ctx->cigar_len.p), n_pairs, static_cast<char*>(ctx->cigars_packed.p));
+    ctx->stats.kernel_launches += 2;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(ctx->h_cigar_begin, d_begin, (n_pairs + 1) * 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    const uint64_t total = static_cast<const uint64_t*>(ctx->h_cigar_begin)[n_pairs];
+    if (total + 1 > ctx->h_cigars_cap) {
+      if (ctx->h_cigars) cudaFreeHost(ctx->h_cigars);
+      ctx->h_cigars = nullptr;
+      ctx->h_cigars_cap = 0;
+      const size_t want = total + total / 4 + 4096;
+      CK(cudaMallocHost(&ctx->h_cigars, want));
+      ctx->h_cigars_cap = want;
+    }
+    if (total) CK(cudaMemcpyAsync(ctx->h_cigars, ctx->cigars_packed.p, total, cudaMemcpyDeviceToHost, st));
+    *packed_out = static_cast<const char*>(ctx->h_cigars);
+    *packed_begin = static_cast<const uint64_t*>(ctx->h_cigar_begin);
+  } else if (cig_bytes) {
+    CK(cudaMemcpyAsync(cigars_out, ctx->cigars.p, cig_bytes, cudaMemcpyDeviceToHost, st));
+  }
   CK(cudaStreamSynchronize(st));
   ctx->stats.n_pairs = n_pairs;
   ctx->stats.n_pairs_wide = n_retry;
@@ -942,4 +1039,33 @@ extern "C" int otgpu_edit_cigars(otgpu_ctx* ctx, const uint8_t* bases, uint64_t 
                                  int32_t* cigar_len_out) {
   return cigars_impl(ctx, bases, n_bases, read_off, read_len, n_reads, pairs, n_pairs, true,
                      AffPen{1, 0, 1, 2, 1}, scores_out, cigars_out, cigar_off, cigar_len_out);
+}
+
+extern "C" int otgpu_affine_cigars_packed(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                                          const uint64_t* read_off, const uint32_t* read_len,
+                                          uint32_t n_reads, const otgpu_pair* pairs, uint64_t n_pairs,
+                                          int mismatch, int gap_open, int gap_ext, int32_t* scores_out,
+                                          int32_t* cigar_len_out, const char** cigars,
+                                          const uint64_t** cigar_begin) {
+  if (mismatch <= 0 || gap_open < 0 || gap_ext <= 0 || !cigars || !cigar_begin) return OTGPU_ERR_ARGS;
+  AffPen pen{mismatch, gap_open, gap_ext, 0, 1};
+  pen.scope = (gap_open + gap_ext > mismatch ? gap_open + gap_ext : mismatch) + 1;
+  {
+    auto gcd = [](int a, int b) { while (b) { const int t = a % b; a = b; b = t; } return a; };
+    pen.step = gcd(gcd(mismatch, gap_open + gap_ext), gap_ext);
+  }
+  if (pen.scope > kAffMaxScope) return OTGPU_ERR_ARGS;
+  return cigars_impl(ctx, bases, n_bases, read_off, read_len, n_reads, pairs, n_pairs, false, pen,
+                     scores_out, nullptr, nullptr, cigar_len_out, cigars, cigar_begin);
+}
+
+extern "C" int otgpu_edit_cigars_packed(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                                        const uint64_t* read_off, const uint32_t* read_len,
+                                        uint32_t n_reads, const otgpu_pair* pairs, uint64_t n_pairs,
+                                        int32_t* scores_out, int32_t* cigar_len_out,
+                                        const char** cigars, const uint64_t** cigar_begin) {
+  if (!cigars || !cigar_begin) return OTGPU_ERR_ARGS;
+  return cigars_impl(ctx, bases, n_bases, read_off, read_len, n_reads, pairs, n_pairs, true,
+                     AffPen{1, 0, 1, 2, 1}, scores_out, nullptr, nullptr, cigar_len_out, cigars,
+                     cigar_begin);
 }

@@ -51,10 +51,25 @@ void batched_cigars(wfa::WFAligner& aligner2, const std::vector<CigarJob>& jobs,
         order.push_back(s);
         total += s->size();
       }
-  void* pinned = nullptr;
-  int st = otgpu_host_alloc(total + 64, &pinned);
-  if (st != OTGPU_OK) die("pinned allocation", st, ctx);
-  uint8_t* bases = static_cast<uint8_t*>(pinned);
+  // pinned staging that lives as long as the calling thread (a pinned allocation per call costs
+  // more than the alignments of a small batch)
+  struct Pinned {
+    void* p = nullptr;
+    size_t cap = 0;
+    ~Pinned() { if (p) otgpu_host_free(p); }
+  };
+  thread_local Pinned pin;
+  int st = OTGPU_OK;
+  if (total + 64 > pin.cap) {
+    if (pin.p) otgpu_host_free(pin.p);
+    pin.p = nullptr;
+    pin.cap = 0;
+    const size_t want = total + total / 4 + 4096;
+    st = otgpu_host_alloc(want, &pin.p);
+    if (st != OTGPU_OK) die("pinned allocation", st, ctx);
+    pin.cap = want;
+  }
+  uint8_t* bases = static_cast<uint8_t*>(pin.p);
   std::vector<uint64_t> off(order.size());
   std::vector<uint32_t> len(order.size());
   uint64_t used = 0;
@@ -65,7 +80,6 @@ void batched_cigars(wfa::WFAligner& aligner2, const std::vector<CigarJob>& jobs,
     used += order[i]->size();
   }
   std::vector<otgpu_pair> pairs(jobs.size());
-  std::vector<uint64_t> coff(jobs.size() + 1, 0);
   for (size_t i = 0; i < jobs.size(); ++i) {
     const CigarJob& j = jobs[i];
     pairs[i].pattern = slot[j.pattern];
@@ -74,22 +88,29 @@ void batched_cigars(wfa::WFAligner& aligner2, const std::vector<CigarJob>& jobs,
     pairs[i].pattern_end_free = j.pb < 0 ? 0 : j.pe;
     pairs[i].text_begin_free = j.pb < 0 ? 0 : j.tb;
     pairs[i].text_end_free = j.pb < 0 ? 0 : j.te;
-    coff[i + 1] = coff[i] + j.pattern->size() + j.text->size();  // a CIGAR is never longer
   }
   std::vector<int32_t> scores(jobs.size()), clen(jobs.size());
-  std::vector<char> cig(cigars ? coff.back() + 1 : 1);  // no CIGAR bytes when only lengths are wanted
-  char* cig_ptr = cigars ? cig.data() : nullptr;
-  const uint64_t* coff_ptr = cigars ? coff.data() : nullptr;
-  st = aligner2.isEdit()
-      ? otgpu_edit_cigars(ctx, bases, used, off.data(), len.data(), (uint32_t)order.size(),
-                          pairs.data(), pairs.size(), scores.data(), cig_ptr, coff_ptr, clen.data())
-      : otgpu_affine_cigars(ctx, bases, used, off.data(), len.data(), (uint32_t)order.size(),
-                            pairs.data(), pairs.size(), aligner2.mismatch(), aligner2.gapOpening(),
-                            aligner2.gapExtension(), scores.data(), cig_ptr, coff_ptr, clen.data());
-  otgpu_host_free(pinned);
+  const char* packed = nullptr;        // context-owned pinned memory, valid until the next call
+  const uint64_t* begin = nullptr;
+  if (cigars) {  // the strings: packed on the device, only their bytes are copied back
+    st = aligner2.isEdit()
+        ? otgpu_edit_cigars_packed(ctx, bases, used, off.data(), len.data(), (uint32_t)order.size(),
+                                   pairs.data(), pairs.size(), scores.data(), clen.data(), &packed, &begin)
+        : otgpu_affine_cigars_packed(ctx, bases, used, off.data(), len.data(), (uint32_t)order.size(),
+                                     pairs.data(), pairs.size(), aligner2.mismatch(),
+                                     aligner2.gapOpening(), aligner2.gapExtension(), scores.data(),
+                                     clen.data(), &packed, &begin);
+  } else {  // scores and lengths only: no CIGAR bytes leave the device
+    st = aligner2.isEdit()
+        ? otgpu_edit_cigars(ctx, bases, used, off.data(), len.data(), (uint32_t)order.size(),
+                            pairs.data(), pairs.size(), scores.data(), nullptr, nullptr, clen.data())
+        : otgpu_affine_cigars(ctx, bases, used, off.data(), len.data(), (uint32_t)order.size(),
+                              pairs.data(), pairs.size(), aligner2.mismatch(), aligner2.gapOpening(),
+                              aligner2.gapExtension(), scores.data(), nullptr, nullptr, clen.data());
+  }
   if (st != OTGPU_OK) die("batched_cigars", st, ctx);
   for (size_t i = 0; i < jobs.size(); ++i) {
-    if (cigars && clen[i] >= 0) (*cigars)[i].assign(cig.data() + coff[i], (size_t)clen[i]);
+    if (cigars && clen[i] >= 0) (*cigars)[i].assign(packed + begin[i], (size_t)clen[i]);
     if (scores_out) (*scores_out)[i] = scores[i];
     if (lengths_out) (*lengths_out)[i] = clen[i] >= 0 ? clen[i] : 0;
   }

@@ -56,6 +56,35 @@ def test_golden_cigars_through_c_abi(ctx, agold):
         assert (int(sc), cg.decode()) == (g["score"], g["cigar"]), (len(g["p"]), len(g["t"]), g["ef"])
 
 
+def test_packed_cigar_output_equals_capacity_layout(ctx, agold):
+    """otgpu_*_cigars_packed: the same scores, lengths and bytes, end to end in pinned memory."""
+    import json
+    import os
+    reads, rows = [], []
+    for g in agold["cigars"]:
+        reads += [u8(g["p"]), u8(g["t"])]
+        rows.append((len(reads) - 2, len(reads) - 1, g["pb"] if g["ef"] else -1, g["pe"], g["tb"], g["te"]))
+    bases, off, lens = S.pack_reads(reads)
+    sc, ln, begin, packed = ctx.cigars_packed(bases, off, lens, PAIRS(rows))
+    assert int(begin[len(rows)]) == int(np.maximum(ln, 0).sum()) == len(packed)
+    for i, g in enumerate(agold["cigars"]):
+        got = packed[int(begin[i]):int(begin[i]) + int(ln[i])].tobytes().decode()
+        assert (int(sc[i]), got) == (g["score"], g["cigar"])
+    eg = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "editcigar_golden.json")))["cigars"]
+    reads, rows = [], []
+    for g in eg:
+        reads += [u8(g["p"]), u8(g["t"])]
+        rows.append((len(reads) - 2, len(reads) - 1, g["pb"] if g["ef"] else -1, g["pe"], g["tb"], g["te"]))
+    bases, off, lens = S.pack_reads(reads)
+    sc, ln, begin, packed = ctx.cigars_packed(bases, off, lens, PAIRS(rows), edit=True)
+    for i, g in enumerate(eg):
+        got = packed[int(begin[i]):int(begin[i]) + int(ln[i])].tobytes().decode()
+        assert (int(sc[i]), got) == (g["score"], g["cigar"])
+    # empty batch
+    sc, ln, begin, packed = ctx.cigars_packed(bases, off, lens, PAIRS([]))
+    assert len(sc) == 0 and len(packed) == 0
+
+
 def test_ppoa_kat_cigars_through_c_abi(ctx, agold):
     for kat in agold["ppoa_kat"]:
         reads = [u8(s) for s in kat["seqs"]]
