@@ -486,7 +486,7 @@ double ref_assemble_regions(const char* bases, const uint64_t* off, const uint32
       });
     });
   };
-  uint32_t wave = 64;
+  uint32_t wave = 100;
   if (const char* e = getenv("OTREF_WAVE")) wave = (uint32_t)atoi(e);
   otb200::run_waves(n_regions, wave, st);
 #endif
