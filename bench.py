@@ -47,6 +47,17 @@ def load_traffic(workload, n_regions):
     return None
 
 
+def load_warp_instructions(workload, n_regions):
+    """Warp instructions per launch of the dominant kernel from the same committed ncu capture."""
+    p = os.path.join(ROOT, "profiles", "r1f_traffic.json")
+    if workload == "C2" and n_regions == synth.CONFIGS["C2"]["n_regions"] and os.path.exists(p):
+        try:
+            return json.load(open(p)).get("warp_instructions")
+        except Exception:
+            pass
+    return None
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -640,6 +651,15 @@ def main():
             "pairs_8bit": stats["n_pairs_8bit"], "pairs_wide": stats["n_pairs_wide"],
             "deterministic": same, "clocks": clocks,
         }
+        wi = load_warp_instructions(args.workload, B["n_regions"])
+        if wi and clocks.get("sm_mhz"):
+            # what actually bounds the kernel: one warp instruction per sub-partition per cycle
+            n_sm = torch.cuda.get_device_properties(local_rank).multi_processor_count
+            peak_i = n_sm * 4 * clocks["sm_mhz"] * 1e6
+            line["roofline"]["issue_slots"] = {
+                "warp_instructions_per_launch": wi, "source": "profiles/r1f_traffic.json (ncu, same workload)",
+                "achieved_per_s": wi / (k_ms * 1e-3), "peak_per_s": peak_i,
+                "frac": wi / (k_ms * 1e-3) / peak_i}
         if world == 1 and not args.no_cpu_baseline:
             base, _, _ = cpu_reference(B, 15.0)
             base.pop("pairs"), base.pop("seconds")

@@ -226,6 +226,31 @@ def test_bad_arguments_are_errors(ctx):
     assert ctx.edit_scores(bases, off, lens, PAIRS([(0, 1, -1, 0, 0, 0)]))[0] == 1
 
 
+def test_maximum_read_length(ctx):
+    """Reads up to the documented limit (2^20 bases; offsets, ring nulls and buffer padding are
+    sized for it) against the port; one base more is an argument error, not a wrong answer."""
+    import otter_b200
+    rng = np.random.default_rng(77)
+    top = 1 << 20
+    a = S.rand_seq(rng, top)
+    b = S.mutate(rng, a, 0.0003)[:top]            # a few hundred edits over a megabase
+    c = S.mutate(rng, a[:300000], 0.001)
+    d = a[:300000].copy()
+    d[1000] = ord("N")                            # 8-bit fallback on a long read
+    reads = [a, b, c, d, a[:300000]]
+    bases, off, lens = S.pack_reads(reads)
+    rows = [(0, 1, -1, 0, 0, 0), (4, 2, -1, 0, 0, 0) if lens[4] >= lens[2] else (2, 4, -1, 0, 0, 0),
+            (3, 4, -1, 0, 0, 0), (0, 4, 0, top - 300000, 0, 0)]
+    pairs = PAIRS(rows)
+    got = ctx.edit_scores(bases, off, lens, pairs)
+    assert np.array_equal(got, port_scores(reads, pairs))
+    assert got[2] == 1
+    too_long = [np.concatenate([a, a[:1]]), a[:10]]
+    bases, off, lens = S.pack_reads(too_long)
+    with pytest.raises(otter_b200.OtgpuError):
+        ctx.edit_scores(bases, off, lens, PAIRS([(0, 1, -1, 0, 0, 0)]))
+
+
 # ---- full-size, size-independent properties ----------------------------------------------------
 def test_full_size_properties(ctx):
     """BASELINE config C1 at 1/10 scale plus structural properties that need no oracle:
