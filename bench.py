@@ -421,6 +421,108 @@ def run_compare(args, rank, world, local_rank):
 
 
 # ------------------------------------------------------------------------------------------------
+def extract_workload(n_regions, reads_per_region, seed):
+    """Synthetic BAM records: per region (2-5 kb wide) long reads (region + 0.5-5 kb either side,
+    10 % of them ending inside the region) with ONT-like CIGARs (an edit every ~20 bases)."""
+    from otter_b200.capi import BAM_READ_DTYPE
+    rng = np.random.default_rng(seed)
+    n = n_regions * reads_per_region
+    rec = np.zeros(n, dtype=BAM_READ_DTYPE)
+    cig_parts, co, so, i = [], 0, 0, 0
+    seq_lens = []
+    for g in range(n_regions):
+        start = 10000 + int(rng.integers(0, 1000000))
+        end = start + int(rng.integers(2000, 5001))
+        for _ in range(reads_per_region):
+            pos = start - int(rng.integers(500, 5000))
+            stop = end + int(rng.integers(500, 5000))
+            if rng.random() < 0.1:
+                stop = start + int(rng.integers(100, end - start))
+            nseg = max(1, (stop - pos) // 20)
+            m = rng.integers(1, 40, nseg).astype(np.uint32)
+            kind = rng.integers(0, 3, nseg)           # 0: M only, 1: M + I, 2: M + D
+            gap = rng.integers(1, 4, nseg).astype(np.uint32)
+            words = np.empty(2 * nseg, dtype=np.uint32)
+            words[0::2] = m << 4
+            words[1::2] = np.where(kind == 1, gap << 4 | 1, np.where(kind == 2, gap << 4 | 2, 0 << 4 | 1))
+            words = words[(words >> 4) > 0]
+            if words[-1] & 0xf:
+                words = words[:-1]
+            ops, lens = words & 0xf, words >> 4
+            l_qseq = int(lens[(ops == 0) | (ops == 1)].sum())
+            rec[i] = (pos, l_qseq, len(words), 0, co, so, start, end)
+            cig_parts.append(words)
+            co += len(words)
+            so += (l_qseq + 1) // 2
+            seq_lens.append(l_qseq)
+            i += 1
+    codes = np.array([1, 2, 4, 8], dtype=np.uint8)
+    seq4 = (codes[rng.integers(0, 4, so)] << 4 | codes[rng.integers(0, 4, so)]).astype(np.uint8)
+    return rec, np.concatenate(cig_parts), seq4
+
+
+def run_extract(args, rank, world, local_rank):
+    """Secondary measurement: get_breakpoints + parse_alignment per BAM record
+    (src/anseqs.cpp:286-436), host records in, extracted reads out."""
+    import ctypes as C
+    if rank != 0:
+        return
+    n_regions = args.regions or 200
+    rec, cig, seq4 = extract_workload(n_regions, 60, 0xE7)
+    n = len(rec)
+    line = {"metric": "BAM records extracted/sec", "unit": "records/s", "n_gpus": 1, "steps": args.steps,
+            "warmup": args.warmup, "higher_is_better": True, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": f"{n_regions} regions x 60 long reads (region + 0.5-5 kb flanks), "
+                                   f"ONT-like CIGARs", "records": n, "cigar_ops": int(len(cig)),
+                       "query_bases": int(rec["l_qseq"].sum())}}
+    flat = np.zeros((n, 8), dtype=np.int64)
+    for k, f in enumerate(("pos", "l_qseq", "n_cigar", "cigar_off", "seq_off")):
+        flat[:, k] = rec[f]
+    flat[:, 6], flat[:, 7] = rec["start"], rec["end"]
+    vp = C.c_void_p
+
+    def reference(threads):
+        lib = C.CDLL(os.path.join(ROOT, "oracle", "_ref", "libotter_ref.so"))
+        lib.ref_parse_alignments_batch.restype = C.c_double
+        lib.ref_parse_alignments_batch.argtypes = [vp, C.c_uint32, vp, vp, C.c_int, vp]
+        out = np.zeros(n, dtype=np.int32)
+        t = lib.ref_parse_alignments_batch(flat.ctypes.data_as(vp), n, cig.ctypes.data_as(vp),
+                                           seq4.ctypes.data_as(vp), threads, out.ctypes.data_as(vp))
+        return t, out
+
+    threads = os.cpu_count() or 1
+    if args.impl == "reference":
+        t = sum(reference(threads)[0] for _ in range(args.steps))
+        line.update(impl="reference", value=n * args.steps / t, ms_per_step=1e3 * t / args.steps,
+                    cpu_baseline={"kind": "reference", "cores": threads, "value": n * args.steps / t,
+                                  "unit": "records/s", "sample": f"all {n} records"})
+        print(json.dumps(line), flush=True)
+        return
+    import otter_b200
+    ctx = otter_b200.Context(local_rank)
+    for _ in range(max(args.warmup, 1)):
+        status, coords, lens, begin, bases = ctx.extract_reads(rec, cig, seq4)
+    l0 = ctx.stats()["kernel_launches"]
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        status, coords, lens, begin, bases = ctx.extract_reads(rec, cig, seq4)
+    t = time.perf_counter() - t0
+    line.update(value=n * args.steps / t, ms_per_step=1e3 * t / args.steps,
+                gpu_launches=int(ctx.stats()["kernel_launches"] - l0),
+                extracted_bases=int(begin[n]),
+                e2e={"value": n * args.steps / t, "unit": "records/s",
+                     "h2d_bytes_per_step": int(rec.nbytes + cig.nbytes + seq4.nbytes),
+                     "d2h_bytes_per_step": int(len(bases) + begin.nbytes + status.nbytes + coords.nbytes + lens.nbytes)})
+    if not args.no_cpu_baseline:
+        tr, out = reference(threads)
+        mine = np.where(status & 1, lens.astype(np.int64), -1)
+        line["cpu_baseline"] = {"kind": "reference", "cores": threads, "value": n / tr, "unit": "records/s",
+                                "sample": f"all {n} records, parse_alignment only"}
+        line["identical_to_reference"] = bool(np.array_equal(mine, out))
+    print(json.dumps(line), flush=True)
+    ctx.close()
+
+
 def run_pipeline(args, rank, world, local_rank):
     """Integration measurement: assemble_process's loop body (src/assemble.cpp:103-142: distance
     matrix -> otter_hclust -> re-assignment -> rapid_consensus) over a wave of regions, host reads
@@ -500,7 +602,7 @@ def main():
     ap.add_argument("--regions", type=int, default=None, help="override regions per GPU")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--path", default="distmatrix", choices=["distmatrix", "consensus", "compare", "pipeline"],
+    ap.add_argument("--path", default="distmatrix", choices=["distmatrix", "consensus", "compare", "pipeline", "extract"],
                     help="distmatrix = fill_dist_matrix (the headline); consensus = the gap-affine "
                          "+ CIGAR alignments rapid_consensus issues (secondary row)")
     args = ap.parse_args()
@@ -515,6 +617,8 @@ def main():
         return
     if args.path == "pipeline":
         return run_pipeline(args, rank, world, local_rank)
+    if args.path == "extract":
+        return run_extract(args, rank, world, local_rank)
     if args.path == "compare":
         run_compare(args, rank, world, local_rank)
         return

@@ -60,6 +60,28 @@ typedef struct {
   int32_t text_end_free;
 } otgpu_pair;
 
+/* One BAM record against one region, as parse_anreads hands it to parse_alignment
+ * (reference src/anseqs.cpp:440-451): core.pos, core.l_qseq, core.n_cigar, the record's CIGAR
+ * (cigar[cigar_off .. +n_cigar), BAM encoding len << 4 | op) and its 4-bit sequence
+ * (seq4[seq_off .. +(l_qseq+1)/2), two bases per byte, high nibble first), and the region
+ * [start, end] (bed.start, bed.end). */
+typedef struct {
+  int32_t pos;
+  int32_t l_qseq;
+  uint32_t n_cigar;
+  uint32_t reserved;
+  uint64_t cigar_off;
+  uint64_t seq_off;
+  int32_t start;
+  int32_t end;
+} otgpu_bam_read;
+
+/* status bits of otgpu_extract_reads */
+#define OTGPU_READ_OK 1u         /* PARSEMSG.successful: the record reaches the region        */
+#define OTGPU_READ_SPAN_L 2u     /* PARSEMSG.spanning_l                                       */
+#define OTGPU_READ_SPAN_R 4u     /* PARSEMSG.spanning_r                                       */
+#define OTGPU_READ_BAD_COORDS 8u /* the reference would exit(1) or read outside the record    */
+
 /* Per-launch work counters (diagnostics for the roofline / issue-bound argument). */
 typedef struct {
   uint64_t n_pairs;
@@ -172,6 +194,23 @@ int otgpu_edit_cigars_packed(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_ba
                              const otgpu_pair* pairs, uint64_t n_pairs, int32_t* scores_out,
                              int32_t* cigar_len_out, const char** cigars,
                              const uint64_t** cigar_begin);
+
+/* ---- batched read extraction ------------------------------------------------------------------ */
+/* get_breakpoints + parse_alignment (reference src/anseqs.cpp:286-436) for a batch of BAM records:
+ * per record the CIGAR is walked on the device, the query is cut to the region and its 4-bit
+ * bases are decoded to characters (seq_nt16_str).  Outputs, all indexed like `reads`:
+ *   status[i]      OTGPU_READ_* bits (records without OTGPU_READ_OK yield nothing);
+ *   coords[2i..]   PARSEMSG.alignment_coords after parse_alignment (what becomes ANREAD.ccoords);
+ *   out_len[i]     length of the extracted sequence ("N" = 1 for a deleted region / empty cut);
+ *   *bases, *begin the sequences packed end to end in pinned memory the context owns (valid
+ *                  until the next call on ctx): record i is (*bases)[(*begin)[i] .. +out_len[i]),
+ *                  (*begin)[n_reads] the total — directly usable as the bases / read_off /
+ *                  read_len arguments of the alignment entry points above.
+ * Record-level filters (mapq, flags, rq; :444,454) stay with the caller. */
+int otgpu_extract_reads(otgpu_ctx* ctx, const otgpu_bam_read* reads, uint32_t n_reads,
+                        const uint32_t* cigar, uint64_t n_cigar_ops, const uint8_t* seq4,
+                        uint64_t n_seq_bytes, uint8_t* status, int32_t* coords, uint32_t* out_len,
+                        const char** bases, const uint64_t** begin);
 
 #ifdef __cplusplus
 }

@@ -43,6 +43,19 @@
 
 // Defined (external linkage, not in the header) at src/analignments.cpp:62.
 double align_anreads(wfa::WFAligner& aligner, ANREAD& read_x, ANREAD& read_y);
+// src/anseqs.cpp:218-227,412: the class is local to that source file, so its declaration is
+// repeated here to reach parse_alignment (members are defined in anseqs.o)
+class PARSEMSG {
+ public:
+  bool successful;
+  bool spanning_l;
+  bool spanning_r;
+  std::pair<int, int> alignment_coords;
+  PARSEMSG();
+  bool is_spanning() const;
+  void transfer_status(ANREAD&) const;
+};
+void parse_alignment(const int& rstart, const int& rend, bam1_t* read, PARSEMSG& msg, std::string& seq);
 
 namespace {
 struct Aligners {
@@ -323,6 +336,87 @@ int ref_assemble_region(const char* bases, const uint64_t* off, const uint32_t* 
   *out_ic = clust.ic;
   for (uint32_t i = 0; i < n_reads; ++i) out_labels[i] = labels[i];
   return clust.fc;
+}
+
+// parse_alignment (src/anseqs.cpp:393-418: get_breakpoints :286-391 + the 4-bit decode) on one
+// synthetic BAM record: pos, BAM-encoded CIGAR (len << 4 | op), query sequence.  Outputs what
+// parse_anreads keeps: msg.successful, the spanning flags, msg.alignment_coords and the extracted
+// sequence.  Returns its length (0 when not successful).
+int ref_parse_alignment(int pos, const uint32_t* cigar, uint32_t n_cigar, const char* seq, int l_qseq,
+                        int start, int end, int* successful, int* span, int* coords, char* out,
+                        int cap) {
+  bam1_t* b = bam_init1();
+  const char qname[4] = "r\0\0";
+  b->core.pos = pos;
+  b->core.l_qname = 4;
+  b->core.n_cigar = n_cigar;
+  b->core.l_qseq = l_qseq;
+  b->l_data = b->m_data = 4 + 4 * (int)n_cigar + (l_qseq + 1) / 2 + l_qseq;
+  b->data = (uint8_t*)calloc(b->m_data + 8, 1);
+  std::memcpy(b->data, qname, 4);
+  std::memcpy(b->data + 4, cigar, 4 * (size_t)n_cigar);
+  uint8_t* t = bam_get_seq(b);
+  for (int i = 0; i < l_qseq; ++i)  // sam.c:598
+    t[i >> 1] |= seq_nt16_table[(unsigned char)seq[i]] << ((~i & 1) << 2);
+  PARSEMSG msg;
+  std::string got;
+  parse_alignment(start, end, b, msg, got);
+  *successful = msg.successful;
+  *span = (msg.spanning_l ? 1 : 0) | (msg.spanning_r ? 2 : 0);
+  coords[0] = msg.alignment_coords.first;
+  coords[1] = msg.alignment_coords.second;
+  bam_destroy1(b);
+  if (!msg.successful) return 0;
+  std::memcpy(out, got.data(), (int)got.size() < cap ? got.size() : cap);
+  return (int)got.size();
+}
+
+// parse_alignment over a batch of records (8 int64 each: pos, l_qseq, n_cigar, cigar_off, seq_off,
+// region, start, end; seq4 already in BAM's 4-bit form) on `threads` host threads, static
+// contiguous blocks.  The bam1_t records are built before the clock starts (htslib hands them to
+// parse_anreads ready-made).  out_len[i] = length of the extracted sequence, -1 if not successful.
+// Returns wall seconds of the parse_alignment calls.
+double ref_parse_alignments_batch(const int64_t* recs, uint32_t n, const uint32_t* cigar,
+                                  const uint8_t* seq4, int threads, int32_t* out_len) {
+  std::vector<bam1_t*> bs(n);
+  for (uint32_t i = 0; i < n; ++i) {
+    const int64_t* r = recs + 8 * (size_t)i;
+    bam1_t* b = bam_init1();
+    b->core.pos = (int32_t)r[0];
+    b->core.l_qseq = (int32_t)r[1];
+    b->core.n_cigar = (uint32_t)r[2];
+    b->core.l_qname = 4;
+    const size_t nb = ((size_t)r[1] + 1) / 2;
+    b->l_data = b->m_data = (int)(4 + 4 * (size_t)r[2] + nb + (size_t)r[1]);
+    b->data = (uint8_t*)calloc((size_t)b->m_data + 8, 1);
+    b->data[0] = 'r';
+    std::memcpy(b->data + 4, cigar + r[3], 4 * (size_t)r[2]);
+    std::memcpy(bam_get_seq(b), seq4 + r[4], nb);
+    bs[i] = b;
+  }
+  if (threads < 1) threads = 1;
+  const auto t0 = std::chrono::steady_clock::now();
+  {
+    std::vector<std::thread> pool;
+    const uint32_t per = (n + threads - 1) / threads;
+    for (int t = 0; t < threads; ++t) {
+      const uint32_t a = (uint32_t)t * per, e = a + per < n ? a + per : n;
+      if (a >= e) break;
+      pool.emplace_back([&, a, e] {
+        for (uint32_t i = a; i < e; ++i) {
+          const int64_t* r = recs + 8 * (size_t)i;
+          PARSEMSG msg;
+          std::string got;
+          parse_alignment((int)r[6], (int)r[7], bs[i], msg, got);
+          out_len[i] = msg.successful ? (int32_t)got.size() : -1;
+        }
+      });
+    }
+    for (auto& th : pool) th.join();
+  }
+  const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  for (bam1_t* b : bs) bam_destroy1(b);
+  return sec;
 }
 
 // ---- many regions through the body of assemble_process, timed --------------------------------

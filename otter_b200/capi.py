@@ -15,7 +15,7 @@ SYMBOLS = [
     "otgpu_batch_upload_regions", "otgpu_batch_upload_pairs", "otgpu_batch_align",
     "otgpu_batch_download", "otgpu_synchronize", "otgpu_last_align_ms", "otgpu_affine_cigars",
     "otgpu_edit_cigars", "otgpu_last_chunk_count", "otgpu_affine_cigars_packed",
-    "otgpu_edit_cigars_packed",
+    "otgpu_edit_cigars_packed", "otgpu_extract_reads",
 ]
 
 
@@ -31,6 +31,24 @@ class Pair(C.Structure):
 
 PAIR_DTYPE = np.dtype([("pattern", "<u4"), ("text", "<u4"), ("pbf", "<i4"), ("pef", "<i4"),
                        ("tbf", "<i4"), ("tef", "<i4")])
+
+
+# otgpu_bam_read (include/otter_b200.h)
+BAM_READ_DTYPE = np.dtype([("pos", "<i4"), ("l_qseq", "<i4"), ("n_cigar", "<u4"), ("reserved", "<u4"),
+                           ("cigar_off", "<u8"), ("seq_off", "<u8"), ("start", "<i4"), ("end", "<i4")])
+NT16 = "=ACMGRSVTWYHKDBN"
+
+
+def encode_seq4(seq):
+    """BAM 4-bit encoding of a base string (two bases per byte, high nibble first)."""
+    table = np.full(256, 15, dtype=np.uint8)
+    for i, ch in enumerate(NT16):
+        table[ord(ch)] = i
+        table[ord(ch.lower())] = i
+    codes = table[np.frombuffer(seq.encode() if isinstance(seq, str) else bytes(seq), dtype=np.uint8)]
+    if len(codes) % 2:
+        codes = np.concatenate([codes, np.zeros(1, np.uint8)])
+    return (codes[0::2] << 4 | codes[1::2]).astype(np.uint8)
 
 
 class Stats(C.Structure):
@@ -79,6 +97,8 @@ def lib():
                                                  C.POINTER(vp), C.POINTER(vp)]
         l.otgpu_edit_cigars_packed.argtypes = [vp, vp, u64, vp, vp, u32, vp, u64, vp, vp,
                                                C.POINTER(vp), C.POINTER(vp)]
+        l.otgpu_extract_reads.argtypes = [vp, vp, u32, vp, u64, vp, u64, vp, vp, vp, C.POINTER(vp),
+                                          C.POINTER(vp)]
         l.otgpu_last_chunk_count.restype = u64
         l.otgpu_last_chunk_count.argtypes = [vp]
         _lib = l
@@ -175,6 +195,28 @@ class Context:
         self._ck(self._l.otgpu_edit_cigars(self._h, _p(bases), bases.size, _p(off), _p(lens), len(lens),
                                            _p(pairs), n, _p(scores), None, None, _p(clen)))
         return scores, clen
+
+    def extract_reads(self, records, cigar, seq4):
+        """get_breakpoints + parse_alignment for a batch of BAM records (BAM_READ_DTYPE) ->
+        (status uint8[n], coords int32[n,2], lens uint32[n], begin uint64[n+1], bases uint8[total]);
+        the last two are views of pinned memory the context owns."""
+        records = np.ascontiguousarray(records, dtype=BAM_READ_DTYPE)
+        cigar = np.ascontiguousarray(cigar, dtype=np.uint32)
+        seq4 = np.ascontiguousarray(seq4, dtype=np.uint8)
+        n = len(records)
+        status = np.zeros(n, dtype=np.uint8)
+        coords = np.zeros((n, 2), dtype=np.int32)
+        lens = np.zeros(n, dtype=np.uint32)
+        pb, pg = C.c_void_p(), C.c_void_p()
+        self._ck(self._l.otgpu_extract_reads(self._h, _p(records), n, _p(cigar), cigar.size, _p(seq4),
+                                             seq4.size, _p(status), _p(coords), _p(lens),
+                                             C.byref(pb), C.byref(pg)))
+        if n == 0 or not pg.value:
+            return status, coords, lens, np.zeros(1, np.uint64), np.zeros(0, np.uint8)
+        begin = np.ctypeslib.as_array(C.cast(pg, C.POINTER(C.c_uint64)), shape=(n + 1,))
+        total = int(begin[n])
+        bases = np.ctypeslib.as_array(C.cast(pb, C.POINTER(C.c_uint8)), shape=(max(total, 1),))[:total]
+        return status, coords, lens, begin, bases
 
     def cigars_packed(self, bases, off, lens, pairs, x=4, o=6, e=2, edit=False):
         """Packed output: -> (scores, lengths, begin uint64[n+1], packed uint8[total]); the last two

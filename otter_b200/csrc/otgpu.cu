@@ -13,6 +13,7 @@
 #include "wfa_edit.cuh"
 #include "wfa_affine.cuh"
 #include "wfa_edit_cigar.cuh"
+#include "bam_extract.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -231,10 +232,15 @@ struct otgpu_ctx {
       scores, ovf_list, counters, wide_ws, order, order_ctl;
   DevBuf aff_rings, aff_slab, aff_slab2, aff_ops, cigar_off, cigars, cigar_len;  // gap-affine path
   DevBuf cigar_begin, cigars_packed;            // packed CIGAR output (device side)
+  DevBuf bam_reads, bam_cigar, bam_seq4, bam_status, bam_coords, bam_plan;  // read extraction
   void* h_cigars = nullptr;                     // pinned: packed CIGARs of the last call
   size_t h_cigars_cap = 0;
   void* h_cigar_begin = nullptr;                // pinned: n_pairs + 1 start offsets
   size_t h_cigar_begin_cap = 0;
+  void* h_reads = nullptr;                      // pinned: extracted reads of the last call
+  size_t h_reads_cap = 0;
+  void* h_read_begin = nullptr;                 // pinned: n_reads + 1 start offsets
+  size_t h_read_begin_cap = 0;
   void* h_pk_off = nullptr;  // pinned
   size_t h_pk_off_cap = 0;
   void* h_counters = nullptr;  // pinned, 4 x u64
@@ -439,13 +445,16 @@ void otgpu_destroy(otgpu_ctx* ctx) {
                     &ctx->packed, &ctx->region_start, &ctx->score_off, &ctx->pairs, &ctx->scores,
                     &ctx->ovf_list, &ctx->counters, &ctx->wide_ws, &ctx->order, &ctx->order_ctl, &ctx->aff_rings,
                     &ctx->aff_slab, &ctx->aff_slab2, &ctx->aff_ops, &ctx->cigar_off, &ctx->cigars,
-                    &ctx->cigar_len, &ctx->cigar_begin, &ctx->cigars_packed};
+                    &ctx->cigar_len, &ctx->cigar_begin, &ctx->cigars_packed, &ctx->bam_reads,
+                    &ctx->bam_cigar, &ctx->bam_seq4, &ctx->bam_status, &ctx->bam_coords, &ctx->bam_plan};
   for (DevBuf* b : bufs)
     if (b->p) cudaFree(b->p);
   if (ctx->h_pk_off) cudaFreeHost(ctx->h_pk_off);
   if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
   if (ctx->h_cigars) cudaFreeHost(ctx->h_cigars);
   if (ctx->h_cigar_begin) cudaFreeHost(ctx->h_cigar_begin);
+  if (ctx->h_reads) cudaFreeHost(ctx->h_reads);
+  if (ctx->h_read_begin) cudaFreeHost(ctx->h_read_begin);
   for (cudaEvent_t e : ctx->ev)
     if (e) cudaEventDestroy(e);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -1068,4 +1077,81 @@ extern "C" int otgpu_edit_cigars_packed(otgpu_ctx* ctx, const uint8_t* bases, ui
   return cigars_impl(ctx, bases, n_bases, read_off, read_len, n_reads, pairs, n_pairs, true,
                      AffPen{1, 0, 1, 2, 1}, scores_out, nullptr, nullptr, cigar_len_out, cigars,
                      cigar_begin);
+}
+
+// ---- batched read extraction (bam_extract.cuh) -------------------------------------------------
+extern "C" int otgpu_extract_reads(otgpu_ctx* ctx, const otgpu_bam_read* reads, uint32_t n_reads,
+                                   const uint32_t* cigar, uint64_t n_cigar_ops, const uint8_t* seq4,
+                                   uint64_t n_seq_bytes, uint8_t* status, int32_t* coords,
+                                   uint32_t* out_len, const char** bases, const uint64_t** begin) {
+  if (!ctx || !bases || !begin) return OTGPU_ERR_ARGS;
+  *bases = nullptr;
+  *begin = nullptr;
+  if (n_reads == 0) return OTGPU_OK;
+  if (!reads || !status || !coords || !out_len || (!cigar && n_cigar_ops) || (!seq4 && n_seq_bytes))
+    return OTGPU_ERR_ARGS;
+  for (uint32_t i = 0; i < n_reads; ++i) {  // every record must lie inside the two arrays
+    const otgpu_bam_read& r = reads[i];
+    if (r.l_qseq < 0 || r.cigar_off > n_cigar_ops || r.n_cigar > n_cigar_ops - r.cigar_off ||
+        r.seq_off > n_seq_bytes || ((uint64_t)r.l_qseq + 1) / 2 > n_seq_bytes - r.seq_off)
+      return OTGPU_ERR_ARGS;
+  }
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  CK(cudaStreamSynchronize(st));
+  RS(bam_reads, (size_t)n_reads * sizeof(otgpu_bam_read));
+  RS(bam_cigar, n_cigar_ops * 4 + 4);
+  RS(bam_seq4, n_seq_bytes + 4);
+  RS(bam_status, n_reads);
+  RS(bam_coords, (size_t)n_reads * 8);
+  RS(bam_plan, (size_t)n_reads * sizeof(ExtractPlan));
+  RS(cigar_len, (size_t)n_reads * 4);          // per-record output lengths (scan input)
+  RS(cigar_begin, ((size_t)n_reads + 1) * 8);  // start offsets
+  if (((size_t)n_reads + 1) * 8 > ctx->h_read_begin_cap) {
+    if (ctx->h_read_begin) cudaFreeHost(ctx->h_read_begin);
+    ctx->h_read_begin = nullptr;
+    ctx->h_read_begin_cap = 0;
+    const size_t want = ((size_t)n_reads + 1) * 8 + n_reads + 4096;
+    CK(cudaMallocHost(&ctx->h_read_begin, want));
+    ctx->h_read_begin_cap = want;
+  }
+  CK(cudaMemcpyAsync(ctx->bam_reads.p, reads, (size_t)n_reads * sizeof(otgpu_bam_read), cudaMemcpyHostToDevice, st));
+  if (n_cigar_ops) CK(cudaMemcpyAsync(ctx->bam_cigar.p, cigar, n_cigar_ops * 4, cudaMemcpyHostToDevice, st));
+  if (n_seq_bytes) CK(cudaMemcpyAsync(ctx->bam_seq4.p, seq4, n_seq_bytes, cudaMemcpyHostToDevice, st));
+  const otgpu_bam_read* d_reads = static_cast<const otgpu_bam_read*>(ctx->bam_reads.p);
+  int32_t* d_len = static_cast<int32_t*>(ctx->cigar_len.p);
+  uint64_t* d_begin = static_cast<uint64_t*>(ctx->cigar_begin.p);
+  ExtractPlan* d_plan = static_cast<ExtractPlan*>(ctx->bam_plan.p);
+  k_bam_breakpoints<<<(n_reads + 255) / 256, 256, 0, st>>>(
+      d_reads, n_reads, static_cast<const uint32_t*>(ctx->bam_cigar.p),
+      static_cast<uint8_t*>(ctx->bam_status.p), static_cast<int32_t*>(ctx->bam_coords.p), d_plan, d_len);
+  k_cigar_scan<<<1, 1024, 0, st>>>(d_len, n_reads, d_begin);
+  ctx->stats.kernel_launches += 2;
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(ctx->h_read_begin, d_begin, ((size_t)n_reads + 1) * 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(status, ctx->bam_status.p, n_reads, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(coords, ctx->bam_coords.p, (size_t)n_reads * 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(out_len, d_len, (size_t)n_reads * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  const uint64_t total = static_cast<const uint64_t*>(ctx->h_read_begin)[n_reads];
+  RS(cigars_packed, total + 16);
+  if (total + 1 > ctx->h_reads_cap) {
+    if (ctx->h_reads) cudaFreeHost(ctx->h_reads);
+    ctx->h_reads = nullptr;
+    ctx->h_reads_cap = 0;
+    const size_t want = total + total / 4 + 4096;
+    CK(cudaMallocHost(&ctx->h_reads, want));
+    ctx->h_reads_cap = want;
+  }
+  if (total) {
+    k_bam_decode<<<ctx->n_sm * 8, 256, 0, st>>>(d_reads, n_reads, static_cast<const uint8_t*>(ctx->bam_seq4.p),
+                                                d_plan, d_len, d_begin, static_cast<char*>(ctx->cigars_packed.p));
+    ctx->stats.kernel_launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(ctx->h_reads, ctx->cigars_packed.p, total, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+  }
+  *bases = static_cast<const char*>(ctx->h_reads);
+  *begin = static_cast<const uint64_t*>(ctx->h_read_begin);
+  return OTGPU_OK;
 }

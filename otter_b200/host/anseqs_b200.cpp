@@ -1,0 +1,75 @@
+// otter_b200/host/anseqs_b200.cpp — see anseqs_b200.hpp.
+#include "anseqs_b200.hpp"
+
+#include <cstdlib>
+#include <cstring>
+#include <iostream>
+
+#include "otter_b200.h"
+
+void ReadExtractor::add(uint32_t region, int start, int end, const BamRecordView& rec) {
+  Rec r;
+  r.pos = rec.pos;
+  r.l_qseq = rec.l_qseq;
+  r.n_cigar = rec.n_cigar;
+  r.region = region;
+  r.cigar_off = cigar_.size();
+  r.seq_off = seq4_.size();
+  r.start = start;
+  r.end = end;
+  cigar_.insert(cigar_.end(), rec.cigar, rec.cigar + rec.n_cigar);
+  const size_t nb = ((size_t)(rec.l_qseq > 0 ? rec.l_qseq : 0) + 1) / 2;
+  seq4_.insert(seq4_.end(), rec.seq4, rec.seq4 + nb);
+  recs_.push_back(r);
+  names_.emplace_back(rec.qname ? rec.qname : "");
+}
+
+void ReadExtractor::extract(wfa::WFAligner& aligner, bool omitnonspanning,
+                            std::vector<std::vector<ANREAD>>& blocks) {
+  const uint32_t n = (uint32_t)recs_.size();
+  if (n == 0) return;
+  otgpu_ctx* ctx = aligner.context();
+  std::vector<otgpu_bam_read> in(n);
+  for (uint32_t i = 0; i < n; ++i) {
+    const Rec& r = recs_[i];
+    in[i] = otgpu_bam_read{r.pos, r.l_qseq, r.n_cigar, 0, r.cigar_off, r.seq_off, r.start, r.end};
+  }
+  std::vector<uint8_t> status(n);
+  std::vector<int32_t> coords(2 * (size_t)n);
+  std::vector<uint32_t> len(n);
+  const char* bases = nullptr;
+  const uint64_t* begin = nullptr;
+  const int st = ctx ? otgpu_extract_reads(ctx, in.data(), n, cigar_.data(), cigar_.size(), seq4_.data(),
+                                           seq4_.size(), status.data(), coords.data(), len.data(),
+                                           &bases, &begin)
+                     : OTGPU_ERR_NO_DEVICE;
+  if (st != OTGPU_OK) {
+    std::cerr << "ERROR: otter_b200 read extraction: " << otgpu_strerror(st) << " ("
+              << (ctx ? otgpu_last_cuda_error(ctx) : "") << ")" << std::endl;
+    exit(1);  // the reference's convention for fatal conditions
+  }
+  for (uint32_t i = 0; i < n; ++i) {
+    const uint8_t s = status[i];
+    if (s & OTGPU_READ_BAD_COORDS) {  // src/anseqs.cpp:418-421
+      std::cerr << "ERROR: unexpected querty start/end coords found for read " << names_[i] << std::endl;
+      exit(1);
+    }
+    if (!(s & OTGPU_READ_OK)) continue;
+    const bool sl = (s & OTGPU_READ_SPAN_L) != 0, sr = (s & OTGPU_READ_SPAN_R) != 0;
+    if (omitnonspanning && !(sl && sr)) continue;  // :451
+    const uint32_t g = recs_[i].region;
+    if (g >= blocks.size()) blocks.resize(g + 1);
+    ANREAD read;
+    read.name = names_[i];
+    read.seq.assign(bases + begin[i], len[i]);
+    if (sl && sr) read.set_is_spanning();  // transfer_status :233-239
+    else if (sl) read.is_spanning_l = true;
+    else if (sr) read.is_spanning_r = true;
+    read.ccoords = {coords[2 * (size_t)i], coords[2 * (size_t)i + 1]};
+    blocks[g].emplace_back(std::move(read));
+  }
+  recs_.clear();
+  cigar_.clear();
+  seq4_.clear();
+  names_.clear();
+}

@@ -6,6 +6,7 @@
 #include <memory>
 
 #include "analignments_b200.hpp"
+#include "anseqs_b200.hpp"
 #include "compare_b200.hpp"
 #include "ppoa_b200.hpp"
 
@@ -169,5 +170,37 @@ int othost_ppoa_cigars(const char* bases, const uint64_t* off, const uint32_t* l
   poa.consensus(consensus);
   if (out && cap > 0) std::memcpy(out, consensus.data(), (int)consensus.size() < cap ? consensus.size() : cap);
   return (int)consensus.size();
+}
+
+// ReadExtractor (anseqs_b200.hpp) over flat arrays: record i = (pos, l_qseq, n_cigar, cigar words
+// at cigar_off, 4-bit bases at seq_off, region id, start, end), 8 int64 per record.  Output per
+// kept read (in region order, then input order): region, span bits, ccoords, length; sequences
+// concatenated in out_bases.  Returns the number of reads kept.
+uint32_t othost_extract_reads(const int64_t* recs, uint32_t n, const uint32_t* cigar, const uint8_t* seq4,
+                              int omitnonspanning, uint32_t n_regions, int32_t* out_meta /*5 per read*/,
+                              char* out_bases, uint64_t cap) {
+  ReadExtractor ex;
+  for (uint32_t i = 0; i < n; ++i) {
+    const int64_t* r = recs + 8 * (size_t)i;
+    BamRecordView v{(int32_t)r[0], (int32_t)r[1], (uint32_t)r[2], cigar + r[3], seq4 + r[4], "r"};
+    ex.add((uint32_t)r[5], (int)r[6], (int)r[7], v);
+  }
+  std::vector<std::vector<ANREAD>> blocks(n_regions);
+  ex.extract(aligner(), omitnonspanning != 0, blocks);
+  uint32_t kept = 0;
+  uint64_t used = 0;
+  for (uint32_t g = 0; g < blocks.size(); ++g)
+    for (const ANREAD& a : blocks[g]) {
+      int32_t* m = out_meta + 5 * (size_t)kept;
+      m[0] = (int32_t)g;
+      m[1] = (a.is_spanning_l ? 1 : 0) | (a.is_spanning_r ? 2 : 0);
+      m[2] = a.ccoords.first;
+      m[3] = a.ccoords.second;
+      m[4] = (int32_t)a.seq.size();
+      if (used + a.seq.size() <= cap) std::memcpy(out_bases + used, a.seq.data(), a.seq.size());
+      used += a.seq.size();
+      ++kept;
+    }
+  return kept;
 }
 }
