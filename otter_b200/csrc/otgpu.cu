@@ -782,17 +782,22 @@ namespace {
 
 // Gap-affine + CIGAR: persistent warps, one pair per warp, per-warp HBM workspace.
 // RETRY = second pass over the pairs whose trace outgrew the first-tier slab.
+constexpr int kRingPad = 32;  // int32: 128 B between the power-of-two rings of a warp
+#ifndef OTGPU_AFF_MIN_CTAS
+#define OTGPU_AFF_MIN_CTAS 1
+#endif
 template <bool RETRY, bool EDIT>
-__global__ void __launch_bounds__(kCtaThreads)
+__global__ void __launch_bounds__(kCtaThreads, OTGPU_AFF_MIN_CTAS)
 k_affine(DevBatch b, Counters* __restrict__ ctr, uint32_t* __restrict__ ovf_list, AffPen pen,
-         int32_t* __restrict__ rings, int wcap, uint8_t* __restrict__ slab, uint32_t slab_bytes,
+         int32_t* __restrict__ rings, int wcap, int n_rings, uint8_t* __restrict__ slab, uint32_t slab_bytes,
          uint8_t* __restrict__ ops, uint32_t ops_cap, const uint64_t* __restrict__ cigar_off,
          char* __restrict__ cigars, int32_t* __restrict__ cigar_len) {
   __shared__ AffSlot meta_smem[kWarpsPerCta][EDIT ? 1 : kAffMaxScope];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const size_t gw = (size_t)blockIdx.x * kWarpsPerCta + warp;
   AffWork W;
-  W.rings = rings + gw * (EDIT ? 2 : 3 * (size_t)pen.scope) * wcap;
+  W.rstride = wcap + kRingPad;
+  W.rings = rings + gw * (size_t)n_rings * W.rstride;
   W.wmask = wcap - 1;
   W.slab = slab + gw * (size_t)slab_bytes;
   W.slab_bytes = slab_bytes;
@@ -919,7 +924,12 @@ int cigars_impl(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const ui
   // per-warp workspace: rings cover every diagonal of the longest pair, so they never alias
   const int wcap = next_pow2(2 * (int)ctx->max_len + 64);
   const uint32_t ops_cap = 4u * ctx->max_len + 64u;
-  const size_t ring_bytes = (size_t)(edit ? 2 : 3 * pen.scope) * wcap * 4;
+  // rings per warp: edit + CIGAR ping-pongs two; gap-affine keeps max(x, o+e)/g + 1 wavefronts of
+  // M and e/g + 1 of I1 and of D1 (wfa_affine.cuh)
+  const int n_rings = edit ? 2
+                           : (pen.x > pen.o + pen.e ? pen.x : pen.o + pen.e) / pen.step + 1 +
+                                 2 * (pen.e / pen.step + 1);
+  const size_t ring_bytes = (size_t)n_rings * (wcap + kRingPad) * 4;
   // first-tier trace slab per warp: edit distance stores one byte per (score, diagonal) of ONE
   // component and its wavefronts are narrower, so half the slab and four times the warps
   const uint32_t slab1 = edit ? (1u << 20) : (2u << 20);
@@ -956,7 +966,7 @@ int cigars_impl(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const ui
   Counters* ctr = static_cast<Counters*>(ctx->counters.p);
   uint32_t* ovf = static_cast<uint32_t*>(ctx->ovf_list.p);
   (edit ? k_affine<false, true> : k_affine<false, false>)<<<grid, kCtaThreads, 0, st>>>(
-      b, ctr, ovf, pen, static_cast<int32_t*>(ctx->aff_rings.p), wcap,
+      b, ctr, ovf, pen, static_cast<int32_t*>(ctx->aff_rings.p), wcap, n_rings,
       static_cast<uint8_t*>(ctx->aff_slab.p), slab1, static_cast<uint8_t*>(ctx->aff_ops.p), ops_cap,
       d_cigar_off, static_cast<char*>(ctx->cigars.p), static_cast<int32_t*>(ctx->cigar_len.p));
   ctx->stats.kernel_launches += 2;
@@ -970,7 +980,7 @@ int cigars_impl(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const ui
     if (grid2 > 8) grid2 = 8;
     RS(aff_slab2, (size_t)grid2 * kWarpsPerCta * slab2);
     (edit ? k_affine<true, true> : k_affine<true, false>)<<<grid2, kCtaThreads, 0, st>>>(
-        b, ctr, ovf, pen, static_cast<int32_t*>(ctx->aff_rings.p), wcap,
+        b, ctr, ovf, pen, static_cast<int32_t*>(ctx->aff_rings.p), wcap, n_rings,
         static_cast<uint8_t*>(ctx->aff_slab2.p), slab2, static_cast<uint8_t*>(ctx->aff_ops.p),
         ops_cap, d_cigar_off, static_cast<char*>(ctx->cigars.p),
         static_cast<int32_t*>(ctx->cigar_len.p));

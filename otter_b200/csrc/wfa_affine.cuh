@@ -31,8 +31,11 @@ struct AffSlot {  // one score slot (score % scope): ranges + flags of M, I1, D1
 };
 
 struct AffWork {        // per-warp workspace in HBM
-  int32_t* rings;       // [3 * scope] rings of (wmask+1) int32: component-major
-  int wmask;
+  int32_t* rings;       // gap-affine: nM rings of M, then nID of I1, then nID of D1 (see below);
+                        // edit + CIGAR: two ping-pong rings
+  int wmask;            // ring index mask (a ring covers every diagonal of the longest pair)
+  int rstride;          // int32 between consecutive rings: wmask + 1 + padding, so that the rings
+                        // of one warp do not fall into the same L1 sets
   uint8_t* slab;        // step table grows from the front (8 B / score), cells from the back
   uint32_t slab_bytes;
   uint8_t* ops;         // reversed op list for the CIGAR replay
@@ -61,28 +64,36 @@ __device__ int wfa_affine_pair(const AffWork& W, AffSlot* __restrict__ meta, con
   const int plen = J.plen, tlen = J.tlen, ak = tlen - plen;
   const bool ef = J.pb >= 0;
   const int scope = pen.scope, mask = W.wmask;
-  const size_t rstride = (size_t)mask + 1;
+  const size_t rstride = (size_t)W.rstride;
+  // Everything below counts score STEPS of g = gcd(x, o+e, e): wavefront t holds score t*g.  M is
+  // read xs = x/g and oes = (o+e)/g steps back, I1/D1 es = e/g steps back, so nM = max(xs,oes)+1
+  // M rings and nID = es+1 rings each of I1 and D1 are live at any time (5 + 2 + 2 for 4/6/2
+  // instead of 3 x 9 score slots: a third of the cache footprint).
+  const int xs = pen.x / pen.step, oes = (pen.o + pen.e) / pen.step, es = pen.e / pen.step;
+  const int nM = (xs > oes ? xs : oes) + 1, nID = es + 1;
   int2* const steps = reinterpret_cast<int2*>(W.slab);  // {lo, cell base} per score
   uint32_t cells_top = W.slab_bytes;                    // cells grow downward from here
-  int score = 0, sm = 0, null_steps = 0, end_k = 0, end_off = 0;  // sm = score % scope
+  int score = 0, sm = 0, si = 0, null_steps = 0, end_k = 0, end_off = 0;  // sm = t % nM, si = t % nID
   // every reachable score is a multiple of g = gcd(x, o+e, e): the scores in between are null
   // steps (wavefront_compute_affine.c:199-206) and are only counted, g at a time
   const int g = pen.step;
 
-#define RING(c, slot) (W.rings + ((size_t)(c)*scope + (slot)) * rstride)
+#define RING_M(slot) (W.rings + (size_t)(slot) * rstride)
+#define RING_I(slot) (W.rings + (size_t)(nM + (slot)) * rstride)
+#define RING_D(slot) (W.rings + (size_t)(nM + nID + (slot)) * rstride)
   // ---- wavefront 0 (wavefront_align.c:113-135 / :190-245) ----
   {
     const int lo0 = ef ? -J.pb : 0, hi0 = ef ? J.tb : 0;
     const int w0 = hi0 - lo0 + 1;
     if ((uint32_t)w0 + 64 > W.slab_bytes || w0 + 8 > mask) return kAffOverflow;
     cells_top -= (uint32_t)w0;
-    int32_t* m0 = RING(0, 0);
+    int32_t* m0 = RING_M(0);
     for (int k = lo0 + lane; k <= hi0; k += 32) {
       m0[k & mask] = k > 0 ? k : 0;
       W.slab[cells_top + (k - lo0)] = 3;  // start cell
     }
     if (lane == 0) {
-      for (int s = 0; s < scope; ++s) meta[s].flags = 0;
+      for (int s = 0; s < nM; ++s) meta[s].flags = 0;
       meta[0].lo[0] = lo0; meta[0].hi[0] = hi0; meta[0].flags = 1;
       steps[0] = make_int2(lo0, (int)cells_top);
     }
@@ -95,7 +106,7 @@ __device__ int wfa_affine_pair(const AffWork& W, AffSlot* __restrict__ meta, con
     if (!(fl & 1)) {
       if (null_steps > scope) return -1;  // WF_STATUS_UNFEASIBLE (:369-372)
     } else {
-      int32_t* m = RING(0, sm);
+      int32_t* m = RING_M(sm);
       WfState S;
       S.lo = meta[sm].lo[0];
       S.hi = meta[sm].hi[0];
@@ -162,16 +173,17 @@ __device__ int wfa_affine_pair(const AffWork& W, AffSlot* __restrict__ meta, con
       if (null_steps > scope) return -1;
     }
     score += g;
-    sm += g;
-    if (sm >= scope) sm -= scope;
+    if (++sm == nM) sm = 0;
+    if (++si == nID) si = 0;
     {
       const int so = sm;
       if ((uint32_t)(score + 1) * 8u + 64u > cells_top) return kAffOverflow;
       const int s_mis = score - pen.x, s_open = score - pen.o - pen.e, s_ext = score - pen.e;
-      // ring slots of the three source scores (each penalty < scope)
-      const int q_mis = so - pen.x + (so < pen.x ? scope : 0);
-      const int q_open = so - pen.o - pen.e + (so < pen.o + pen.e ? scope : 0);
-      const int q_ext = so - pen.e + (so < pen.e ? scope : 0);
+      // ring slots of the three source wavefronts
+      const int q_mis = so - xs + (so < xs ? nM : 0);
+      const int q_open = so - oes + (so < oes ? nM : 0);
+      const int q_ext = so - es + (so < es ? nM : 0);  // M slot (and meta) of score - e
+      const int qi_ext = si - es + (si < es ? nID : 0);  // I1/D1 ring of score - e
       // usable input = exists and not ->null (wavefront_compute.c:88-95); else lo=1, hi=-1
       int mm_lo = 1, mm_hi = -1, mo_lo = 1, mo_hi = -1, ie_lo = 1, ie_hi = -1, de_lo = 1, de_hi = -1;
       bool has_mm = false, has_mo = false, has_ie = false, has_de = false;
@@ -207,13 +219,13 @@ __device__ int wfa_affine_pair(const AffWork& W, AffSlot* __restrict__ meta, con
       if ((uint32_t)(score + 1) * 8u + 64u + (uint32_t)width > cells_top) return kAffOverflow;
       cells_top -= (uint32_t)width;
       const bool has_i = has_mo || has_ie, has_d = has_mo || has_de;  // wavefront_compute.c:262-283
-      const int32_t* r_mm = RING(0, q_mis);
-      const int32_t* r_mo = RING(0, q_open);
-      const int32_t* r_ie = RING(1, q_ext);
-      const int32_t* r_de = RING(2, q_ext);
-      int32_t* o_m = RING(0, so);
-      int32_t* o_i = RING(1, so);
-      int32_t* o_d = RING(2, so);
+      const int32_t* r_mm = RING_M(q_mis);
+      const int32_t* r_mo = RING_M(q_open);
+      const int32_t* r_ie = RING_I(qi_ext);
+      const int32_t* r_de = RING_D(qi_ext);
+      int32_t* o_m = RING_M(so);
+      int32_t* o_i = RING_I(si);
+      int32_t* o_d = RING_D(si);
       int mn[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff};
       int mx[3] = {(int)0x80000000, (int)0x80000000, (int)0x80000000};
       for (int kc = lo; kc <= hi; kc += 32) {
@@ -324,7 +336,9 @@ backtrace:
     if (score_out) *score_out = -result;
     return len;
   }
-#undef RING
+#undef RING_M
+#undef RING_I
+#undef RING_D
 }
 
 }  // namespace otgpu

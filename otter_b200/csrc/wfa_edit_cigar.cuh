@@ -32,7 +32,7 @@ __device__ int wfa_editcigar_pair(const AffWork& W, const EditJob& J, const int 
   const bool ef = J.pb >= 0;
   const int mask = W.wmask;
   int32_t* cur = W.rings;
-  int32_t* nxt = W.rings + ((size_t)mask + 1);
+  int32_t* nxt = W.rings + (size_t)W.rstride;
   int2* const steps = reinterpret_cast<int2*>(W.slab);  // {lo, cell base} per score
   uint32_t cells_top = W.slab_bytes;                    // cells grow downward from here
   int score = 0, end_k = 0, end_off = 0;
