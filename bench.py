@@ -499,7 +499,16 @@ def run_extract(args, rank, world, local_rank):
         print(json.dumps(line), flush=True)
         return
     import otter_b200
+    from otter_b200.capi import PinnedArray
     ctx = otter_b200.Context(local_rank)
+    # pinned host staging: the buffers a host integration fills while iterating the BAM
+    # (ReadExtractor::add copies each record's CIGAR and 4-bit bases out of htslib's buffer anyway)
+    pins = []
+    for a in (rec, cig, seq4):
+        pa = PinnedArray(a.shape, a.dtype)
+        pa.array[...] = a
+        pins.append(pa)
+    rec, cig, seq4 = (pa.array for pa in pins)
     for _ in range(max(args.warmup, 1)):
         status, coords, lens, begin, bases = ctx.extract_reads(rec, cig, seq4)
     l0 = ctx.stats()["kernel_launches"]

@@ -7,6 +7,32 @@
 
 #include "otter_b200.h"
 
+template <class T>
+PinnedBuf<T>::~PinnedBuf() {
+  if (p_) otgpu_host_free(p_);
+}
+
+template <class T>
+void PinnedBuf<T>::append(const T* src, size_t n) {
+  if (size_ + n > cap_) {
+    const size_t want = (size_ + n) * 2 + 4096;
+    void* q = nullptr;
+    const int st = otgpu_host_alloc(want * sizeof(T), &q);
+    if (st != OTGPU_OK) {  // no device or no memory: there is no CPU path to fall back to
+      std::cerr << "ERROR: otter_b200 read extraction: pinned allocation: " << otgpu_strerror(st) << std::endl;
+      exit(1);
+    }
+    if (size_) std::memcpy(q, p_, size_ * sizeof(T));
+    if (p_) otgpu_host_free(p_);
+    p_ = static_cast<T*>(q);
+    cap_ = want;
+  }
+  if (n) std::memcpy(p_ + size_, src, n * sizeof(T));
+  size_ += n;
+}
+template class PinnedBuf<uint32_t>;
+template class PinnedBuf<uint8_t>;
+
 void ReadExtractor::add(uint32_t region, int start, int end, const BamRecordView& rec) {
   Rec r;
   r.pos = rec.pos;
@@ -17,9 +43,9 @@ void ReadExtractor::add(uint32_t region, int start, int end, const BamRecordView
   r.seq_off = seq4_.size();
   r.start = start;
   r.end = end;
-  cigar_.insert(cigar_.end(), rec.cigar, rec.cigar + rec.n_cigar);
+  cigar_.append(rec.cigar, rec.n_cigar);
   const size_t nb = ((size_t)(rec.l_qseq > 0 ? rec.l_qseq : 0) + 1) / 2;
-  seq4_.insert(seq4_.end(), rec.seq4, rec.seq4 + nb);
+  seq4_.append(rec.seq4, nb);
   recs_.push_back(r);
   names_.emplace_back(rec.qname ? rec.qname : "");
 }

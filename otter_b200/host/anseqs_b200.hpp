@@ -23,6 +23,25 @@ struct BamRecordView {
   const char* qname;
 };
 
+// Grow-only array in pinned host memory (otgpu_host_alloc): the record data goes to the device
+// at PCIe speed instead of through the driver's pageable staging.
+template <class T>
+class PinnedBuf {
+ public:
+  PinnedBuf() {}
+  PinnedBuf(const PinnedBuf&) = delete;
+  PinnedBuf& operator=(const PinnedBuf&) = delete;
+  ~PinnedBuf();
+  void append(const T* src, size_t n);
+  void clear() { size_ = 0; }
+  size_t size() const { return size_; }
+  const T* data() const { return p_; }
+
+ private:
+  T* p_ = nullptr;
+  size_t size_ = 0, cap_ = 0;
+};
+
 // Accumulates the records of a wave of regions, then extracts them all at once.
 class ReadExtractor {
  public:
@@ -39,7 +58,7 @@ class ReadExtractor {
  private:
   struct Rec { int32_t pos, l_qseq; uint32_t n_cigar, region; uint64_t cigar_off, seq_off; int32_t start, end; };
   std::vector<Rec> recs_;
-  std::vector<uint32_t> cigar_;
-  std::vector<uint8_t> seq4_;
+  PinnedBuf<uint32_t> cigar_;
+  PinnedBuf<uint8_t> seq4_;
   std::vector<std::string> names_;
 };
