@@ -212,6 +212,18 @@ int otgpu_extract_reads(otgpu_ctx* ctx, const otgpu_bam_read* reads, uint32_t n_
                         uint64_t n_seq_bytes, uint8_t* status, int32_t* coords, uint32_t* out_len,
                         const char** bases, const uint64_t** begin);
 
+/* ---- kernel density estimates for the clustering cut ------------------------------------------ */
+/* KDE::f (reference src/ankde.cpp:9-23) as otter_find_clustering_dist uses it
+ * (src/otterclust.cpp:20-29): for every region g the density of its pairwise distances
+ * values[value_off[g] .. value_off[g+1]) with bandwidth[g], at the n_grid abscissae of `grid`
+ * (the caller builds them the way the reference does: x = 0, x += 0.0025 while x <= 1).
+ * densities_out[g * n_grid + i] = f(grid[i]), bit-identical to the host computation (same
+ * summation order, IEEE operations, the host libm's exp: exp_host_libm.cuh).  n_regions <= 65535
+ * per call. */
+int otgpu_kde_densities(otgpu_ctx* ctx, const double* values, const uint64_t* value_off,
+                        uint32_t n_regions, const double* bandwidth, const double* grid,
+                        uint32_t n_grid, double* densities_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -26,6 +26,7 @@
 #endif
 #include "andistmat.hpp"
 #include "anfahelper.hpp"
+#include "ankde.hpp"
 #include "anppoa.hpp"
 #include "anseqs.hpp"
 #include "otterclust.hpp"
@@ -417,6 +418,41 @@ double ref_parse_alignments_batch(const int64_t* recs, uint32_t n, const uint32_
   const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   for (bam1_t* b : bs) bam_destroy1(b);
   return sec;
+}
+
+// KDE::f (src/ankde.cpp:19-23) over a grid built as otter_find_clustering_dist builds it
+// (src/otterclust.cpp:25-28): out[i] = kde.f(x_i), x_0 = 0, x_{i+1} = x_i + dinterval while <= 1.
+// Returns the number of grid points.
+int ref_kde_densities(const double* values, uint64_t n, double bandwidth, double dinterval, double* out,
+                      int cap) {
+  KDE kde(bandwidth);
+  for (uint64_t i = 0; i < n; ++i) kde.values.emplace_back(values[i]);
+  int k = 0;
+  for (double x = 0.0; x <= 1.0; x += dinterval) {
+    const double f = kde.f(x);
+    if (k < cap) out[k] = f;
+    ++k;
+  }
+  return k;
+}
+
+// otter_hclust (src/otterclust.cpp:118-320) on one distance matrix; read lengths stand in for the
+// reads (only seq.size() is used).  Outputs labels (per valid read), ic, fc.
+void ref_otter_hclust(const double* dist, uint32_t n, const uint32_t* read_len, int max_alleles,
+                      int* labels, int* ic, int* fc) {
+  std::vector<ANREAD> reads(n);
+  std::vector<int> indeces(n);
+  for (uint32_t i = 0; i < n; ++i) {
+    reads[i].seq.assign(read_len[i], 'A');
+    indeces[i] = (int)i;
+  }
+  DistMatrix dm(n);
+  for (size_t i = 0; i < dm.values.size(); ++i) dm.values[i] = dist[i];
+  ClusteringStatus clust;
+  otter_hclust(true, max_alleles, 0.01, 500, 0.015, 0.01, 0.2, 500, 0.1, indeces, dm, tls().edit, reads, clust);
+  for (uint32_t i = 0; i < n; ++i) labels[i] = clust.labels[i];
+  *ic = clust.ic;
+  *fc = clust.fc;
 }
 
 // ---- many regions through the body of assemble_process, timed --------------------------------

@@ -15,7 +15,7 @@ SYMBOLS = [
     "otgpu_batch_upload_regions", "otgpu_batch_upload_pairs", "otgpu_batch_align",
     "otgpu_batch_download", "otgpu_synchronize", "otgpu_last_align_ms", "otgpu_affine_cigars",
     "otgpu_edit_cigars", "otgpu_last_chunk_count", "otgpu_affine_cigars_packed",
-    "otgpu_edit_cigars_packed", "otgpu_extract_reads",
+    "otgpu_edit_cigars_packed", "otgpu_extract_reads", "otgpu_kde_densities",
 ]
 
 
@@ -99,6 +99,7 @@ def lib():
                                                C.POINTER(vp), C.POINTER(vp)]
         l.otgpu_extract_reads.argtypes = [vp, vp, u32, vp, u64, vp, u64, vp, vp, vp, C.POINTER(vp),
                                           C.POINTER(vp)]
+        l.otgpu_kde_densities.argtypes = [vp, vp, vp, u32, vp, vp, u32, vp]
         l.otgpu_last_chunk_count.restype = u64
         l.otgpu_last_chunk_count.argtypes = [vp]
         _lib = l
@@ -195,6 +196,18 @@ class Context:
         self._ck(self._l.otgpu_edit_cigars(self._h, _p(bases), bases.size, _p(off), _p(lens), len(lens),
                                            _p(pairs), n, _p(scores), None, None, _p(clen)))
         return scores, clen
+
+    def kde_densities(self, values, value_off, bandwidth, grid):
+        """KDE::f at every grid point for every region -> float64[n_regions, n_grid]."""
+        values = np.ascontiguousarray(values, dtype=np.float64)
+        value_off = np.ascontiguousarray(value_off, dtype=np.uint64)
+        bandwidth = np.ascontiguousarray(bandwidth, dtype=np.float64)
+        grid = np.ascontiguousarray(grid, dtype=np.float64)
+        n = len(value_off) - 1
+        out = np.zeros((n, len(grid)), dtype=np.float64)
+        self._ck(self._l.otgpu_kde_densities(self._h, _p(values), _p(value_off), n, _p(bandwidth), _p(grid),
+                                             len(grid), _p(out)))
+        return out
 
     def extract_reads(self, records, cigar, seq4):
         """get_breakpoints + parse_alignment for a batch of BAM records (BAM_READ_DTYPE) ->

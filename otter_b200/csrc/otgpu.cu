@@ -14,7 +14,9 @@
 #include "wfa_affine.cuh"
 #include "wfa_edit_cigar.cuh"
 #include "bam_extract.cuh"
+#include "kde.cuh"
 
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -233,6 +235,7 @@ struct otgpu_ctx {
   DevBuf aff_rings, aff_slab, aff_slab2, aff_ops, cigar_off, cigars, cigar_len;  // gap-affine path
   DevBuf cigar_begin, cigars_packed;            // packed CIGAR output (device side)
   DevBuf bam_reads, bam_cigar, bam_seq4, bam_status, bam_coords, bam_plan;  // read extraction
+  DevBuf kde_values, kde_off, kde_grid, kde_h, kde_inv_h, kde_out;          // density estimates
   void* h_cigars = nullptr;                     // pinned: packed CIGARs of the last call
   size_t h_cigars_cap = 0;
   void* h_cigar_begin = nullptr;                // pinned: n_pairs + 1 start offsets
@@ -446,7 +449,9 @@ void otgpu_destroy(otgpu_ctx* ctx) {
                     &ctx->ovf_list, &ctx->counters, &ctx->wide_ws, &ctx->order, &ctx->order_ctl, &ctx->aff_rings,
                     &ctx->aff_slab, &ctx->aff_slab2, &ctx->aff_ops, &ctx->cigar_off, &ctx->cigars,
                     &ctx->cigar_len, &ctx->cigar_begin, &ctx->cigars_packed, &ctx->bam_reads,
-                    &ctx->bam_cigar, &ctx->bam_seq4, &ctx->bam_status, &ctx->bam_coords, &ctx->bam_plan};
+                    &ctx->bam_cigar, &ctx->bam_seq4, &ctx->bam_status, &ctx->bam_coords, &ctx->bam_plan,
+                    &ctx->kde_values, &ctx->kde_off, &ctx->kde_grid, &ctx->kde_h, &ctx->kde_inv_h,
+                    &ctx->kde_out};
   for (DevBuf* b : bufs)
     if (b->p) cudaFree(b->p);
   if (ctx->h_pk_off) cudaFreeHost(ctx->h_pk_off);
@@ -1163,5 +1168,54 @@ extern "C" int otgpu_extract_reads(otgpu_ctx* ctx, const otgpu_bam_read* reads, 
   }
   *bases = static_cast<const char*>(ctx->h_reads);
   *begin = static_cast<const uint64_t*>(ctx->h_read_begin);
+  return OTGPU_OK;
+}
+
+// ---- kernel density estimates (kde.cuh) ---------------------------------------------------------
+extern "C" int otgpu_kde_densities(otgpu_ctx* ctx, const double* values, const uint64_t* value_off,
+                                   uint32_t n_regions, const double* bandwidth, const double* grid,
+                                   uint32_t n_grid, double* densities_out) {
+  if (!ctx) return OTGPU_ERR_ARGS;
+  if (n_regions == 0 || n_grid == 0) return OTGPU_OK;
+  if (!value_off || !bandwidth || !grid || !densities_out) return OTGPU_ERR_ARGS;
+  const uint64_t n_values = value_off[n_regions];
+  if (value_off[0] != 0 || (!values && n_values)) return OTGPU_ERR_ARGS;
+  for (uint32_t g = 0; g < n_regions; ++g)
+    if (value_off[g + 1] < value_off[g] || !(bandwidth[g] > 0.0)) return OTGPU_ERR_ARGS;
+  std::vector<double> inv_h;
+  try {
+    inv_h.resize(n_regions);
+  } catch (...) {
+    return OTGPU_ERR_OOM;
+  }
+  for (uint32_t g = 0; g < n_regions; ++g) inv_h[g] = 1 / bandwidth[g];  // KDE::k_h, ankde.cpp:14-17
+  const double pi = 3.14159265358979323846;                             // ankde.hpp:17
+  const double c1 = 1 / std::sqrt(2 * pi);                               // KDE::k, ankde.cpp:9-12
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  CK(cudaStreamSynchronize(st));
+  RS(kde_values, n_values * 8 + 8);
+  RS(kde_off, ((size_t)n_regions + 1) * 8);
+  RS(kde_grid, (size_t)n_grid * 8);
+  RS(kde_h, (size_t)n_regions * 8);
+  RS(kde_inv_h, (size_t)n_regions * 8);
+  RS(kde_out, (size_t)n_regions * n_grid * 8);
+  if (n_values) CK(cudaMemcpyAsync(ctx->kde_values.p, values, n_values * 8, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->kde_off.p, value_off, ((size_t)n_regions + 1) * 8, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->kde_grid.p, grid, (size_t)n_grid * 8, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->kde_h.p, bandwidth, (size_t)n_regions * 8, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->kde_inv_h.p, inv_h.data(), (size_t)n_regions * 8, cudaMemcpyHostToDevice, st));
+  CK(cudaStreamSynchronize(st));  // inv_h leaves scope
+  const dim3 grid_dim((n_grid + 127) / 128, n_regions);
+  k_kde<<<grid_dim, 128, 0, st>>>(static_cast<const double*>(ctx->kde_values.p),
+                                  static_cast<const uint64_t*>(ctx->kde_off.p),
+                                  static_cast<const double*>(ctx->kde_grid.p), (int)n_grid,
+                                  static_cast<const double*>(ctx->kde_h.p),
+                                  static_cast<const double*>(ctx->kde_inv_h.p), c1,
+                                  static_cast<double*>(ctx->kde_out.p));
+  ctx->stats.kernel_launches++;
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(densities_out, ctx->kde_out.p, (size_t)n_regions * n_grid * 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
   return OTGPU_OK;
 }
