@@ -590,7 +590,7 @@ def run_pipeline(args, rank, world, local_rank):
                 e2e={"value": n_regions * args.steps / t, "unit": "regions/s",
                      "h2d_bytes_per_step": int(B["bases"].nbytes), "d2h_bytes_per_step": None},
                 note="host reads -> alleles; GPU: all alignments (batched per wave); host threads: the "
-                     "reference's otter_hclust, partial-order consensus (otter_b200/host/ppoa_b200.hpp)")
+                     "clustering logic + hclust-cpp (densities from the GPU), partial-order consensus (ppoa_b200.hpp)")
     if not args.no_cpu_baseline:
         R = min(n_regions, max(threads * 2, 32))
         tr, labels, n_al, dig = run(bind("libotter_ref.so"), R)

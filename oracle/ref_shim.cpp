@@ -20,6 +20,7 @@
 #include "bindings/cpp/WFAligner.hpp"
 #ifdef OTTER_B200_IN_TREE
 #include "analignments_b200.hpp"
+#include "otterclust_b200.hpp"
 #include "wave_b200.hpp"
 #else
 #include "analignments.hpp"
@@ -29,7 +30,9 @@
 #include "ankde.hpp"
 #include "anppoa.hpp"
 #include "anseqs.hpp"
+#ifndef OTTER_B200_IN_TREE  // (no include guard in that header; otterclust_b200.hpp brings it in-tree)
 #include "otterclust.hpp"
+#endif
 
 #include <chrono>
 #include <cstdint>
@@ -449,7 +452,12 @@ void ref_otter_hclust(const double* dist, uint32_t n, const uint32_t* read_len, 
   DistMatrix dm(n);
   for (size_t i = 0; i < dm.values.size(); ++i) dm.values[i] = dist[i];
   ClusteringStatus clust;
+#ifdef OTTER_B200_IN_TREE  // the same call through the batched, device-assisted restatement
+  std::vector<HclustJob> jobs{{&indeces, &dm, &reads, &clust}};
+  otter_hclust_batch(true, max_alleles, 0.01, 500, 0.015, 0.01, 0.2, 500, 0.1, tls().edit, jobs, 1);
+#else
   otter_hclust(true, max_alleles, 0.01, 500, 0.015, 0.01, 0.2, 500, 0.1, indeces, dm, tls().edit, reads, clust);
+#endif
   for (uint32_t i = 0; i < n; ++i) labels[i] = clust.labels[i];
   *ic = clust.ic;
   *fc = clust.fc;
@@ -569,6 +577,9 @@ double ref_assemble_regions(const char* bases, const uint64_t* off, const uint32
     parallel_blocks(b - a, threads, [&](uint32_t i) { f(a + i); });
   };
   std::vector<ConsensusJob> cjobs(n_regions);  // one slot per region (unused when no valid read)
+  std::vector<std::vector<double>> dens(n_regions);
+  std::vector<double> bandw(n_regions, 0.01);
+  const bool host_kde = getenv("OTREF_HOST_KDE") != nullptr;  // A/B: the reference's own otter_hclust
   otb200::WaveStages st;
   st.device1 = [&](uint32_t a, uint32_t b) {
     timed("build reads", [&] { blocks(a, b, prepare); });
@@ -579,9 +590,35 @@ double ref_assemble_regions(const char* bases, const uint64_t* off, const uint32
         if (!W[g].valid.empty()) jobs.push_back({&W[g].reads, &W[g].valid, W[g].dm.get()});
       fill_dist_matrices(ignore_haps, A.edit, jobs);
     });
+    if (!host_kde) timed("density estimates (GPU)", [&] {
+      std::vector<HclustJob> jobs;
+      std::vector<uint32_t> owner;
+      for (uint32_t g = a; g < b; ++g)
+        if (!W[g].valid.empty()) {
+          jobs.push_back({&W[g].valid, W[g].dm.get(), &W[g].reads, &W[g].clust});
+          owner.push_back(g);
+        }
+      std::vector<std::vector<double>> d;
+      std::vector<double> h;
+      hclust_densities(max_alleles, 0.01, 500, 0.015, A.edit, jobs, d, h);
+      for (size_t i = 0; i < owner.size(); ++i) {
+        dens[owner[i]] = std::move(d[i]);
+        bandw[owner[i]] = h[i];
+      }
+    });
   };
   st.host1 = [&](uint32_t a, uint32_t b) {
-    timed("otter_hclust (host)", [&] { blocks(a, b, [&](uint32_t g) { cluster(g, A.edit); }); });
+    timed("otter_hclust (host)", [&] {
+      blocks(a, b, [&](uint32_t g) {
+        if (host_kde) return cluster(g, A.edit);
+        RegionWork& w = W[g];
+        if (w.valid.empty()) return;
+        HclustJob job{&w.valid, w.dm.get(), &w.reads, &w.clust};
+        hclust_finish(max_alleles, 0.01, 0.2, 500, 0.1, job, dens[g], bandw[g]);
+        for (uint32_t i = 0; i < w.clust.labels.size(); ++i) w.labels[w.valid[i]] = w.clust.labels[i];
+        w.alleles.resize(w.clust.fc);
+      });
+    });
   };
   st.device2 = [&](uint32_t a, uint32_t b) {
     timed("re-assignment + consensus alignments (GPU)", [&] {
