@@ -249,11 +249,18 @@ void rapid_consensus_alignments(wfa::WFAligner& aligner2, std::vector<ConsensusJ
   affine_cigars(aligner2, cj, cigars);
   // getAlignmentCigar() after a skipped call returns the previous alignment's CIGAR (:280): replay
   // that with a running "last CIGAR", in the order a single reference thread would have run
-  std::string last = aligner2.getAlignmentCigar();
+  // (each CIGAR is moved to its plan, not copied: they are the bulk of the host-side bytes)
+  const std::string initial = aligner2.getAlignmentCigar();
+  const std::string* last = &initial;
   size_t q = 0;
   for (const Ref& r : refs) {
-    if (r.aligned) last = cigars[q++];
-    jobs[r.job].plans[r.label].cigars[r.member] = last;
+    std::string& slot = jobs[r.job].plans[r.label].cigars[r.member];
+    if (r.aligned) {
+      slot = std::move(cigars[q++]);
+      last = &slot;
+    } else {
+      slot = *last;
+    }
   }
 }
 
