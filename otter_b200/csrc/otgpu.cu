@@ -914,7 +914,11 @@ int cigars_impl(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const ui
   if (n_pairs == 0) return OTGPU_OK;
   std::vector<uint64_t> own_off;
   if (packed) {  // capacity slots on the device only: a CIGAR is never longer than |pattern|+|text|
-    own_off.resize(n_pairs + 1);
+    try {
+      own_off.resize(n_pairs + 1);
+    } catch (...) {  // nothing may be thrown across the C ABI
+      return OTGPU_ERR_OOM;
+    }
     own_off[0] = 0;
     for (uint64_t i = 0; i < n_pairs; ++i)
       own_off[i + 1] = own_off[i] + read_len[pairs[i].pattern] + read_len[pairs[i].text];
