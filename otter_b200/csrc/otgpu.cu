@@ -793,7 +793,8 @@ constexpr int kRingPad = 32;  // int32: 128 B between the power-of-two rings of 
 #endif
 template <bool RETRY, bool EDIT>
 __global__ void __launch_bounds__(kCtaThreads, OTGPU_AFF_MIN_CTAS)
-k_affine(DevBatch b, Counters* __restrict__ ctr, uint32_t* __restrict__ ovf_list, AffPen pen,
+k_affine(DevBatch b, Counters* __restrict__ ctr, const uint32_t* __restrict__ order,
+         uint32_t* __restrict__ ovf_list, AffPen pen,
          int32_t* __restrict__ rings, int wcap, int n_rings, uint8_t* __restrict__ slab, uint32_t slab_bytes,
          uint8_t* __restrict__ ops, uint32_t ops_cap, const uint64_t* __restrict__ cigar_off,
          char* __restrict__ cigars, int32_t* __restrict__ cigar_len) {
@@ -814,7 +815,7 @@ k_affine(DevBatch b, Counters* __restrict__ ctr, uint32_t* __restrict__ ovf_list
     if (lane == 0) q = atomicAdd(&ctr->v[RETRY ? 2 : 0], 1ull);
     q = __shfl_sync(kFull, q, 0);
     if (q >= limit) break;
-    const uint64_t idx = RETRY ? ovf_list[q] : q;
+    const uint64_t idx = RETRY ? ovf_list[q] : order[q];  // first pass: heaviest pairs first
     const otgpu_pair pr = b.pairs[idx];
     EditJob J;
     J.plen = (int)b.read_len[pr.pattern];
@@ -974,8 +975,19 @@ int cigars_impl(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const ui
   k_pack_reads<<<n_reads, 128, 0, st>>>(b, static_cast<uint32_t*>(ctx->packed.p));
   Counters* ctr = static_cast<Counters*>(ctx->counters.p);
   uint32_t* ovf = static_cast<uint32_t*>(ctx->ovf_list.p);
+  uint32_t* order = static_cast<uint32_t*>(ctx->order.p);
+  {  // heaviest-first queue order, as for the score-only kernel: the last wave of warps is short
+    OrderCtl* ctl = static_cast<OrderCtl*>(ctx->order_ctl.p);
+    CK(cudaMemsetAsync(ctl, 0, sizeof(OrderCtl), st));
+    const int g = (int)((n_pairs + 255) / 256 < (uint64_t)ctx->n_sm * 8 ? (n_pairs + 255) / 256
+                                                                         : (uint64_t)ctx->n_sm * 8);
+    k_order_count<<<g, 256, 0, st>>>(b.pairs, n_pairs, b.read_len, ctl);
+    k_order_scan<<<1, 1, 0, st>>>(ctl);
+    k_order_scatter<<<g, 256, 0, st>>>(b.pairs, n_pairs, b.read_len, ctl, order);
+    ctx->stats.kernel_launches += 3;
+  }
   (edit ? k_affine<false, true> : k_affine<false, false>)<<<grid, kCtaThreads, 0, st>>>(
-      b, ctr, ovf, pen, static_cast<int32_t*>(ctx->aff_rings.p), wcap, n_rings,
+      b, ctr, order, ovf, pen, static_cast<int32_t*>(ctx->aff_rings.p), wcap, n_rings,
       static_cast<uint8_t*>(ctx->aff_slab.p), slab1, static_cast<uint8_t*>(ctx->aff_ops.p), ops_cap,
       d_cigar_off, static_cast<char*>(ctx->cigars.p), static_cast<int32_t*>(ctx->cigar_len.p));
   ctx->stats.kernel_launches += 2;
@@ -989,7 +1001,7 @@ int cigars_impl(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const ui
     if (grid2 > 8) grid2 = 8;
     RS(aff_slab2, (size_t)grid2 * kWarpsPerCta * slab2);
     (edit ? k_affine<true, true> : k_affine<true, false>)<<<grid2, kCtaThreads, 0, st>>>(
-        b, ctr, ovf, pen, static_cast<int32_t*>(ctx->aff_rings.p), wcap, n_rings,
+        b, ctr, order, ovf, pen, static_cast<int32_t*>(ctx->aff_rings.p), wcap, n_rings,
         static_cast<uint8_t*>(ctx->aff_slab2.p), slab2, static_cast<uint8_t*>(ctx->aff_ops.p),
         ops_cap, d_cigar_off, static_cast<char*>(ctx->cigars.p),
         static_cast<int32_t*>(ctx->cigar_len.p));
