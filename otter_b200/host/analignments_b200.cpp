@@ -5,10 +5,13 @@
 // result with the reference's own expressions, so dissimilarities are bit-identical.
 #include "analignments_b200.hpp"
 
+#include <algorithm>
 #include <cstdint>
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
+#include <thread>
+#include <vector>
 
 #include "otter_b200.h"
 
@@ -137,12 +140,31 @@ void fill_dist_matrices(const bool& ignore_haps, wfa::WFAligner& aligner,
   std::vector<uint32_t> region_start(jobs.size() + 1, 0);
   std::vector<uint64_t> score_off(jobs.size(), 0);
   uint64_t n_scores = 0;
+  std::vector<const std::string*> seqs;
   for (size_t g = 0; g < jobs.size(); ++g) {
-    for (int i : *jobs[g].indeces) S.add((*jobs[g].reads)[i].seq);
+    for (int i : *jobs[g].indeces) {  // lay the reads out; the bytes are copied below
+      const std::string& q = (*jobs[g].reads)[i].seq;
+      S.off.push_back(S.used);
+      S.len.push_back((uint32_t)q.size());
+      S.used += q.size();
+      seqs.push_back(&q);
+    }
     region_start[g + 1] = (uint32_t)S.off.size();
     score_off[g] = n_scores;
     const uint64_t n = jobs[g].indeces->size();
     n_scores += n * (n ? n - 1 : 0) / 2;
+  }
+  {  // the copy into pinned staging is the longest host step of a wave: a few threads share it
+    const int workers = total > ((size_t)8 << 20) ? 4 : 1;
+    auto copy = [&](size_t a, size_t b) {
+      for (size_t r = a; r < b; ++r) std::memcpy(S.bases + S.off[r], seqs[r]->data(), seqs[r]->size());
+    };
+    std::vector<std::thread> pool;
+    const size_t per = (seqs.size() + workers - 1) / workers;
+    for (int t = 1; t < workers; ++t)
+      if ((size_t)t * per < seqs.size()) pool.emplace_back(copy, (size_t)t * per, std::min(seqs.size(), (size_t)(t + 1) * per));
+    copy(0, std::min(seqs.size(), per));
+    for (auto& th : pool) th.join();
   }
   std::vector<int32_t> scores(n_scores);
   if (all_spanning) {
@@ -156,13 +178,16 @@ void fill_dist_matrices(const bool& ignore_haps, wfa::WFAligner& aligner,
       auto& idx = *jobs[g].indeces;
       auto& reads = *jobs[g].reads;
       const int32_t* sc = scores.data() + score_off[g];
+      // (i,j) in this order is the order of the condensed store itself (src/andistmat.cpp:15-21),
+      // so element q is written directly instead of through set_dist's index arithmetic
+      double* out = jobs[g].distmatrix->values.data();
       size_t q = 0;
       for (uint32_t i = 0; i < idx.size(); ++i)
         for (uint32_t j = i + 1; j < idx.size(); ++j, ++q) {
           const size_t lx = reads[idx[i]].seq.size(), ly = reads[idx[j]].seq.size();
           const double largest = lx < ly ? (double)ly : (double)lx;  // :68
           // equal strings score 0, and 0/largest == 0.0 == the :64 shortcut
-          jobs[g].distmatrix->set_dist(i, j, sc[q] / largest);       // :71-72
+          out[q] = sc[q] / largest;                                  // :71-72
         }
     }
     return;
