@@ -1193,7 +1193,7 @@ extern "C" int otgpu_kde_densities(otgpu_ctx* ctx, const double* values, const u
                                    uint32_t n_grid, double* densities_out) {
   if (!ctx) return OTGPU_ERR_ARGS;
   if (n_regions == 0 || n_grid == 0) return OTGPU_OK;
-  if (!value_off || !bandwidth || !grid || !densities_out) return OTGPU_ERR_ARGS;
+  if (!value_off || !bandwidth || !grid || !densities_out || n_regions > 65535u) return OTGPU_ERR_ARGS;
   const uint64_t n_values = value_off[n_regions];
   if (value_off[0] != 0 || (!values && n_values)) return OTGPU_ERR_ARGS;
   for (uint32_t g = 0; g < n_regions; ++g)
