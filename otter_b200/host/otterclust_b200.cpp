@@ -3,11 +3,14 @@
 #include "otterclust_b200.hpp"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdlib>
+#include <cstring>
 #include <iostream>
 #include <thread>
 #include <utility>
 
+#include "../csrc/exp_host_libm.cuh"
 #include "fastcluster.h"
 #include "otter_b200.h"
 
@@ -112,6 +115,29 @@ Bound decision_bound(const int radius, std::vector<double>& dens) {
   return {at(maxs[first]), at(maxs[second]), at(mins[middle])};
 }
 
+// The device evaluates exp with the roundings of glibc's FMA variant (csrc/exp_host_libm.cuh).
+// If this host's libm rounds differently (no FMA, another libm), device and host densities could
+// differ in the last bit and move a cut: checked once, on the KDE's own range of arguments, and
+// refused loudly rather than answered differently.
+void check_host_exp_once() {
+  static const bool ok = [] {
+    static const uint64_t tab[256] = {
+#include "../csrc/exp_table.inc"
+    };
+    uint64_t seed = 0x9E3779B97F4A7C15ull;
+    for (int i = 0; i < 20000; ++i) {
+      seed = seed * 6364136223846793005ull + 1442695040888963407ull;
+      const double t = (double)(seed >> 11) / 9007199254740992.0 * 42.0;  // |x - v| / h up to 42
+      volatile double x = -(t * t / 2);
+      const double a = std::exp(x), b = otb200::exp_host_libm(x, tab);
+      if (std::memcmp(&a, &b, sizeof a) != 0) return false;
+    }
+    return true;
+  }();
+  if (!ok) fatal("otter_b200: this host's exp() is not the one the device KDE reproduces "
+                 "(glibc >= 2.28 with FMA); use the reference otter_hclust on this machine");
+}
+
 bool needs_kde(const HclustJob& job, int max_alleles) {
   return job.indeces->size() >= 3 && max_alleles != 1;
 }
@@ -122,6 +148,7 @@ void hclust_densities(const int& max_alleles, const double& bandwidth_short, con
                       const double& bandwidth_long, wfa::WFAligner& aligner,
                       const std::vector<HclustJob>& jobs, std::vector<std::vector<double>>& densities,
                       std::vector<double>& bandwidths) {
+  check_host_exp_once();
   const std::vector<double>& grid = kde_grid();
   densities.assign(jobs.size(), std::vector<double>());
   bandwidths.assign(jobs.size(), bandwidth_short);
