@@ -30,6 +30,7 @@
 #include "ankde.hpp"
 #include "anppoa.hpp"
 #include "anseqs.hpp"
+#include "fastcluster.h"
 #ifndef OTTER_B200_IN_TREE  // (no include guard in that header; otterclust_b200.hpp brings it in-tree)
 #include "otterclust.hpp"
 #endif
@@ -461,6 +462,16 @@ void ref_otter_hclust(const double* dist, uint32_t n, const uint32_t* read_len, 
   for (uint32_t i = 0; i < n; ++i) labels[i] = clust.labels[i];
   *ic = clust.ic;
   *fc = clust.fc;
+}
+
+// hclust-cpp as otter calls it (src/otterclust.cpp:183-187,226,241): average linkage on a copy of
+// the condensed matrix, then both cuts.  merge: 2(n-1) ints, height: n-1, labels_k / labels_h: n.
+void ref_hclust_average(const double* dist, int n, int k, double cut, int* merge, double* height,
+                        int* labels_k, int* labels_h) {
+  std::vector<double> copy(dist, dist + (size_t)n * (n - 1) / 2);
+  hclust_fast(n, copy.data(), HCLUST_METHOD_AVERAGE, merge, height);
+  cutree_k(n, merge, k, labels_k);
+  cutree_cdist(n, merge, height, cut, labels_h);
 }
 
 // ---- many regions through the body of assemble_process, timed --------------------------------

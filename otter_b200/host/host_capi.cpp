@@ -8,6 +8,7 @@
 #include "analignments_b200.hpp"
 #include "anseqs_b200.hpp"
 #include "compare_b200.hpp"
+#include "linkage_b200.hpp"
 #include "ppoa_b200.hpp"
 
 namespace {
@@ -202,5 +203,14 @@ uint32_t othost_extract_reads(const int64_t* recs, uint32_t n, const uint32_t* c
       ++kept;
     }
   return kept;
+}
+
+// linkage_b200.hpp: average linkage on a copy of the condensed matrix + both cuts (host only).
+void othost_hclust_average(const double* dist, int n, int k, double cut, int* merge, double* height,
+                           int* labels_k, int* labels_h) {
+  std::vector<double> copy(dist, dist + (size_t)n * (n - 1) / 2);
+  otb200::average_linkage(n, copy.data(), merge, height);
+  otb200::cut_tree_k(n, merge, k, labels_k);
+  otb200::cut_tree_height(n, merge, height, cut, labels_h);
 }
 }
