@@ -11,7 +11,7 @@
 #include <utility>
 
 #include "../csrc/exp_host_libm.cuh"
-#include "fastcluster.h"
+#include "linkage_b200.hpp"
 #include "otter_b200.h"
 
 namespace {
@@ -223,9 +223,9 @@ void hclust_finish(const int& max_alleles, const double& max_tolerable_diff, con
   // average linkage on a copy of the matrix, cut at the decision bound (:180-188)
   std::vector<int> labels(n), merge(2 * (n - 1));
   std::vector<double> height(n - 1), copy = dm.values;
-  hclust_fast(n, copy.data(), HCLUST_METHOD_AVERAGE, merge.data(), height.data());
+  otb200::average_linkage(n, copy.data(), merge.data(), height.data());
   const double cut = bound.dist1 == bandwidth ? bound.dist1 : bound.cut0 + 0.0025;
-  cutree_cdist(n, merge.data(), height.data(), cut, labels.data());
+  otb200::cut_tree_height(n, merge.data(), height.data(), cut, labels.data());
   int n_clusters = 0;
   for (int i = 0; i < n; ++i) n_clusters = std::max(n_clusters, labels[i]);
   ++n_clusters;
@@ -244,11 +244,11 @@ void hclust_finish(const int& max_alleles, const double& max_tolerable_diff, con
     for (int l = 0; l < n_clusters; ++l) (count[l] < need[l] ? outliers : seeds).push_back(l);
     if (seeds.empty()) {  // nothing is covered well enough: cut into max_alleles as is (:224-230)
       std::vector<int> again(n);
-      cutree_k(n, merge.data(), max_alleles, again.data());
+      otb200::cut_tree_k(n, merge.data(), max_alleles, again.data());
       labels = again;
       out.fc = max_alleles;
     } else if ((int)seeds.size() > max_alleles) {  // :240-243
-      cutree_k(n, merge.data(), max_alleles, labels.data());
+      otb200::cut_tree_k(n, merge.data(), max_alleles, labels.data());
       out.fc = max_alleles;
     } else {
       // seeds are renumbered 0.., reads of outlier clusters join the cluster of their nearest

@@ -4,10 +4,10 @@
 // otter_hclust spends its time in KDE::f: 401 grid points x n(n-1)/2 distances x one exp per
 // region.  Here the densities of every region of the wave come from ONE launch
 // (otgpu_kde_densities, bit-identical to the host computation: csrc/kde.cuh), and the rest —
-// normalisation, maxima / minima, the decision bound, average-linkage clustering (hclust-cpp,
-// unchanged), the cut and the coverage-based relabelling — runs per region on the host in the
-// reference's order of operations.  In-tree only: it needs otter's ClusteringStatus and
-// hclust-cpp's fastcluster.
+// normalisation, maxima / minima, the decision bound, average-linkage clustering and the tree
+// cuts (linkage_b200.hpp, bit-identical to hclust-cpp's hclust_fast / cutree_cdist / cutree_k),
+// the coverage-based relabelling — runs per region on the host in the reference's order of
+// operations.  In-tree only: it needs otter's ClusteringStatus (src/otterclust.hpp:7-14).
 #pragma once
 #ifdef OTTER_B200_IN_TREE
 #include <vector>
