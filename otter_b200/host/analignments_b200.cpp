@@ -113,6 +113,56 @@ void fill_dist_matrix(const bool& ignore_haps, wfa::WFAligner& aligner, std::vec
   fill_dist_matrices(ignore_haps, aligner, one);
 }
 
+// Estimated alignment work of one region: the wavefront work of a pair grows with the product of
+// the two lengths at a given divergence, so sum |x|*|y| over the pairs = ((sum l)^2 - sum l^2) / 2.
+std::vector<int> partition_regions_by_work(const std::vector<RegionDistJob>& jobs, int n_parts,
+                                           std::vector<double>* loads) {
+  std::vector<int> part(jobs.size(), 0);
+  std::vector<double> load(n_parts > 0 ? n_parts : 1, 0.0);
+  if (n_parts > 1) {
+    std::vector<std::pair<double, size_t>> work(jobs.size());
+    for (size_t g = 0; g < jobs.size(); ++g) {
+      double sum = 0.0, sq = 0.0;
+      for (int i : *jobs[g].indeces) {
+        const double l = (double)(*jobs[g].reads)[i].seq.size();
+        sum += l;
+        sq += l * l;
+      }
+      work[g] = {(sum * sum - sq) / 2, g};
+    }
+    // heaviest region first, each to the least loaded part (ties: lower index, so it is stable)
+    std::stable_sort(work.begin(), work.end(),
+                     [](const auto& a, const auto& b) { return a.first > b.first; });
+    for (const auto& w : work) {
+      int best = 0;
+      for (int p = 1; p < n_parts; ++p)
+        if (load[p] < load[best]) best = p;
+      part[w.second] = best;
+      load[best] += w.first;
+    }
+  }
+  if (loads) *loads = load;
+  return part;
+}
+
+void fill_dist_matrices_multi(const bool& ignore_haps, std::vector<wfa::WFAligner*>& aligners,
+                              std::vector<RegionDistJob>& jobs) {
+  if (aligners.empty()) die("fill_dist_matrices_multi", OTGPU_ERR_ARGS, nullptr);
+  if (aligners.size() == 1 || !ignore_haps) return fill_dist_matrices(ignore_haps, *aligners[0], jobs);
+  for (auto* a : aligners)
+    if (!a || !a->context()) die("fill_dist_matrices_multi", OTGPU_ERR_NO_DEVICE, nullptr);
+  const std::vector<int> part = partition_regions_by_work(jobs, (int)aligners.size());
+  std::vector<std::vector<RegionDistJob>> share(aligners.size());
+  for (size_t g = 0; g < jobs.size(); ++g) share[part[g]].push_back(jobs[g]);
+  // one host thread per device; the staging buffers are per thread, the contexts per aligner
+  std::vector<std::thread> pool;
+  for (size_t d = 1; d < aligners.size(); ++d)
+    if (!share[d].empty())
+      pool.emplace_back([&, d] { fill_dist_matrices(ignore_haps, *aligners[d], share[d]); });
+  if (!share[0].empty()) fill_dist_matrices(ignore_haps, *aligners[0], share[0]);
+  for (auto& th : pool) th.join();
+}
+
 void fill_dist_matrices(const bool& ignore_haps, wfa::WFAligner& aligner,
                         std::vector<RegionDistJob>& jobs) {
   if (!ignore_haps) {  // haplotag rule only, no alignment (:108-114)

@@ -32,6 +32,19 @@ struct RegionDistJob {
 void fill_dist_matrices(const bool& ignore_haps, wfa::WFAligner& aligner,
                         std::vector<RegionDistJob>& jobs);
 
+// The same over several devices of one box from ONE host process: `aligners`
+// holds one WFAlignerEdit per device (WFAligner::setDefaultDevice(d) before constructing it).
+// Regions are independent, so the jobs are partitioned across the aligners by estimated work
+// (greedy longest-processing-time over sum of |x|*|y| per region), each share runs
+// fill_dist_matrices on its own host thread / device, and every job's DistMatrix is filled in
+// place: the gather is the host memory the caller already owns, there is no collective.  Results
+// do not depend on the partition.
+void fill_dist_matrices_multi(const bool& ignore_haps, std::vector<wfa::WFAligner*>& aligners,
+                              std::vector<RegionDistJob>& jobs);
+// Which aligner each job goes to (exposed for tests): loads[] receives the per-aligner estimate.
+std::vector<int> partition_regions_by_work(const std::vector<RegionDistJob>& jobs, int n_parts,
+                                           std::vector<double>* loads = nullptr);
+
 struct RegionReassignJob {
   std::vector<ANREAD>* reads;
   std::vector<int>* labels;

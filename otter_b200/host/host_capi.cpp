@@ -76,6 +76,63 @@ void othost_fill_dist_matrices(const char* bases, const uint64_t* off, const uin
       std::memcpy(out + out_off[g], dms[g].values.data(), dms[g].values.size() * sizeof(double));
 }
 
+// The same over n_aligners aligners from this one process: aligner a is bound to device
+// devices[a] (several may name the same device).  part_out (optional) receives the aligner of
+// each region.
+void othost_fill_dist_matrices_multi(const char* bases, const uint64_t* off, const uint32_t* len,
+                                     const uint32_t* region_start, uint32_t n_regions,
+                                     const int* devices, int n_aligners, double* out,
+                                     const uint64_t* out_off, int* part_out) {
+  std::vector<std::vector<ANREAD>> reads(n_regions);
+  std::vector<std::vector<int>> idx(n_regions);
+  std::vector<DistMatrix> dms;
+  dms.reserve(n_regions);
+  std::vector<RegionDistJob> jobs;
+  for (uint32_t g = 0; g < n_regions; ++g) {
+    reads[g] = build_reads(bases, off, len, nullptr, region_start[g], region_start[g + 1]);
+    idx[g].resize(reads[g].size());
+    for (size_t i = 0; i < idx[g].size(); ++i) idx[g][i] = (int)i;
+    dms.emplace_back((uint32_t)reads[g].size());
+  }
+  for (uint32_t g = 0; g < n_regions; ++g) jobs.push_back({&reads[g], &idx[g], &dms[g]});
+  std::vector<std::unique_ptr<wfa::WFAlignerEdit>> own;
+  std::vector<wfa::WFAligner*> aligners;
+  for (int a = 0; a < n_aligners; ++a) {
+    wfa::WFAligner::setDefaultDevice(devices[a]);
+    own.emplace_back(new wfa::WFAlignerEdit(wfa::WFAligner::Score, wfa::WFAligner::MemoryMed));
+    aligners.push_back(own.back().get());
+  }
+  wfa::WFAligner::setDefaultDevice(0);
+  if (part_out) {
+    const std::vector<int> part = partition_regions_by_work(jobs, n_aligners);
+    for (uint32_t g = 0; g < n_regions; ++g) part_out[g] = part[g];
+  }
+  fill_dist_matrices_multi(true, aligners, jobs);
+  for (uint32_t g = 0; g < n_regions; ++g)
+    if (!dms[g].values.empty())
+      std::memcpy(out + out_off[g], dms[g].values.data(), dms[g].values.size() * sizeof(double));
+}
+
+// The partition alone (no device needed): part_out[g] = share of region g, loads_out[p] = the
+// estimated work of share p.
+void othost_partition_regions(const uint32_t* len, const uint32_t* region_start, uint32_t n_regions,
+                              int n_parts, int* part_out, double* loads_out) {
+  std::vector<std::vector<ANREAD>> reads(n_regions);
+  std::vector<std::vector<int>> idx(n_regions);
+  std::vector<RegionDistJob> jobs;
+  for (uint32_t g = 0; g < n_regions; ++g) {
+    for (uint32_t r = region_start[g]; r < region_start[g + 1]; ++r) {
+      reads[g].emplace_back("r", std::string(len[r], 'A'));
+      idx[g].push_back((int)(r - region_start[g]));
+    }
+  }
+  for (uint32_t g = 0; g < n_regions; ++g) jobs.push_back({&reads[g], &idx[g], nullptr});
+  std::vector<double> loads;
+  const std::vector<int> part = partition_regions_by_work(jobs, n_parts, &loads);
+  for (uint32_t g = 0; g < n_regions; ++g) part_out[g] = part[g];
+  for (int p = 0; p < n_parts && loads_out; ++p) loads_out[p] = loads[p];
+}
+
 void othost_invalid_reassignment(const char* bases, const uint64_t* off, const uint32_t* len,
                                  const uint8_t* span, uint32_t n_reads, double min_sim,
                                  double max_error, int total_alleles, int* labels) {

@@ -40,8 +40,42 @@ def test_library_is_built_for_sm_100a(built):
 def test_host_layer_exports(built):
     l = C.CDLL(os.path.join(ROOT, "otter_b200", "lib", "libotter_b200_host.so"))
     for s in ("othost_fill_dist_matrix", "othost_fill_dist_matrices", "othost_invalid_reassignment",
-              "othost_align_anreads", "othost_have_device"):
+              "othost_align_anreads", "othost_have_device", "othost_fill_dist_matrices_multi",
+              "othost_partition_regions"):
         assert hasattr(l, s)
+
+
+def test_partition_regions_by_work(built):
+    """fill_dist_matrices_multi's split of regions over devices: every region goes
+    to exactly one share, the greedy heaviest-first rule is reproduced, shares are balanced."""
+    import numpy as np
+    l = C.CDLL(os.path.join(ROOT, "otter_b200", "lib", "libotter_b200_host.so"))
+    vp = C.c_void_p
+    l.othost_partition_regions.argtypes = [vp, vp, C.c_uint32, C.c_int, vp, vp]
+    rng = np.random.default_rng(5)
+    n_reads = rng.integers(0, 40, 300).astype(np.uint32)
+    rs = np.zeros(301, np.uint32)
+    rs[1:] = np.cumsum(n_reads)
+    lens = rng.integers(1, 6000, int(rs[-1])).astype(np.uint32)
+    work = np.zeros(300)
+    for g in range(300):
+        x = lens[rs[g]:rs[g + 1]].astype(np.float64)
+        work[g] = (x.sum() ** 2 - (x * x).sum()) / 2
+    for parts in (1, 2, 8):
+        part = np.full(300, -1, np.int32)
+        loads = np.zeros(parts)
+        l.othost_partition_regions(lens.ctypes.data, rs.ctypes.data, 300, parts, part.ctypes.data,
+                                   loads.ctypes.data)
+        exp_part = np.zeros(300, np.int32)
+        exp_load = np.zeros(parts)
+        if parts > 1:
+            for g in sorted(range(300), key=lambda g: -work[g]):  # stable: ties keep region order
+                p = int(np.argmin(exp_load))
+                exp_part[g] = p
+                exp_load[p] += work[g]
+            assert np.allclose(loads, exp_load)
+            assert loads.max() <= 1.05 * loads.mean()
+        assert np.array_equal(part, exp_part)
 
 
 def test_no_device_means_error_not_fallback(built):

@@ -41,7 +41,36 @@ def host_lib():
     l.othost_fill_dist_matrices.argtypes = [vp, vp, vp, vp, vp, C.c_uint32, vp, vp]
     l.othost_invalid_reassignment.argtypes = [vp, vp, vp, vp, C.c_uint32, C.c_double, C.c_double,
                                               C.c_int, vp]
+    l.othost_fill_dist_matrices_multi.argtypes = [vp, vp, vp, vp, C.c_uint32, vp, C.c_int, vp, vp, vp]
     return l
+
+
+def test_host_layer_multi_device_equals_single(built):
+    """fill_dist_matrices_multi (one process, one aligner per device, regions split by work, no
+    collective) fills the same matrices as one aligner.  With one GPU the aligners share device 0
+    (two contexts, two host threads); with more, every device of the box takes a share."""
+    import otter_b200
+    H = host_lib()
+    rng = np.random.default_rng(81)
+    regions = [S.tr_region(rng, int(n), int(l), e, extra_frac=0.3)
+               for n, l, e in zip(rng.integers(1, 14, 40), rng.integers(200, 1500, 40),
+                                  rng.choice([0.005, 0.05], 40))]
+    B = S.region_batch(regions)
+    one = np.zeros(B["n_scores"])
+    H.othost_fill_dist_matrices(S.ptr(B["bases"]), S.ptr(B["off"]), S.ptr(B["lens"]), None,
+                                S.ptr(B["region_start"]), len(regions), S.ptr(one),
+                                S.ptr(B["score_off"]))
+    n_dev = otter_b200.lib().otgpu_device_count()
+    layouts = [[0, 0], [0, 0, 0]] + ([list(range(n_dev))] if n_dev > 1 else [])
+    for devices in layouts:
+        dev = np.array(devices, np.int32)
+        got = np.full(B["n_scores"], -7.0)
+        part = np.full(len(regions), -1, np.int32)
+        H.othost_fill_dist_matrices_multi(S.ptr(B["bases"]), S.ptr(B["off"]), S.ptr(B["lens"]),
+                                          S.ptr(B["region_start"]), len(regions), S.ptr(dev),
+                                          len(devices), S.ptr(got), S.ptr(B["score_off"]), S.ptr(part))
+        assert np.array_equal(got, one), devices
+        assert set(part.tolist()) == set(range(len(devices)))  # every aligner took a share
 
 
 # ---- C ABI vs golden ---------------------------------------------------------------------------
