@@ -591,6 +591,9 @@ double ref_assemble_regions(const char* bases, const uint64_t* off, const uint32
   std::vector<std::vector<double>> dens(n_regions);
   std::vector<double> bandw(n_regions, 0.01);
   const bool host_kde = getenv("OTREF_HOST_KDE") != nullptr;  // A/B: the reference's own otter_hclust
+  // the second device stage is issued from its own thread (wave_b200.hpp): its own edit aligner,
+  // kept for the life of the process like the thread's other aligners (a context is not free)
+  static wfa::WFAlignerEdit edit2(wfa::WFAligner::Score, wfa::WFAligner::MemoryMed);
   otb200::WaveStages st;
   st.device1 = [&](uint32_t a, uint32_t b) {
     timed("build reads", [&] { blocks(a, b, prepare); });
@@ -637,7 +640,7 @@ double ref_assemble_regions(const char* bases, const uint64_t* off, const uint32
       for (uint32_t g = a; g < b; ++g)
         if (!W[g].valid.empty() && !W[g].invalid.empty())
           rjobs.push_back({&W[g].reads, &W[g].labels, W[g].clust.fc});
-      if (!rjobs.empty()) invalid_reassignments(ignore_haps, 0.9, 0.01, A.edit, rjobs);
+      if (!rjobs.empty()) invalid_reassignments(ignore_haps, 0.9, 0.01, edit2, rjobs);
       std::vector<ConsensusJob> batch;
       std::vector<uint32_t> owner;
       for (uint32_t g = a; g < b; ++g) {
@@ -666,7 +669,9 @@ double ref_assemble_regions(const char* bases, const uint64_t* off, const uint32
   };
   uint32_t wave = 100;
   if (const char* e = getenv("OTREF_WAVE")) wave = (uint32_t)atoi(e);
-  otb200::run_waves(n_regions, wave, st);
+  int issuers = 1;
+  if (const char* e = getenv("OTREF_ISSUERS")) issuers = atoi(e);
+  otb200::run_waves(n_regions, wave, st, issuers);
 #endif
   return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }

@@ -10,9 +10,11 @@
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
+#include <mutex>
 #include <thread>
 #include <vector>
 
+#include "device_turn.hpp"
 #include "otter_b200.h"
 
 namespace {
@@ -219,10 +221,14 @@ void fill_dist_matrices(const bool& ignore_haps, wfa::WFAligner& aligner,
   std::vector<int32_t> scores(n_scores);
   if (all_spanning) {
     // every pair is alignEnd2End(longer, shorter): pairs are expanded on the device
-    int st = otgpu_region_edit_scores(ctx, S.bases, S.used, S.off.data(), S.len.data(),
-                                      (uint32_t)S.off.size(), region_start.data(),
-                                      (uint32_t)jobs.size(), score_off.data(), n_scores,
-                                      scores.data());
+    int st;
+    {
+      std::lock_guard<otb200::DeviceTurn> turn(otb200::device_turn(aligner.device()));
+      st = otgpu_region_edit_scores(ctx, S.bases, S.used, S.off.data(), S.len.data(),
+                                    (uint32_t)S.off.size(), region_start.data(),
+                                    (uint32_t)jobs.size(), score_off.data(), n_scores,
+                                    scores.data());
+    }
     if (st != OTGPU_OK) die("fill_dist_matrix", st, ctx);
     for (size_t g = 0; g < jobs.size(); ++g) {
       auto& idx = *jobs[g].indeces;
@@ -266,8 +272,12 @@ void fill_dist_matrices(const bool& ignore_haps, wfa::WFAligner& aligner,
       }
   }
   std::vector<int32_t> sc(pairs.size());
-  int st = otgpu_edit_scores(ctx, S.bases, S.used, S.off.data(), S.len.data(),
-                             (uint32_t)S.off.size(), pairs.data(), pairs.size(), sc.data());
+  int st;
+  {
+    std::lock_guard<otb200::DeviceTurn> turn(otb200::device_turn(aligner.device()));
+    st = otgpu_edit_scores(ctx, S.bases, S.used, S.off.data(), S.len.data(),
+                           (uint32_t)S.off.size(), pairs.data(), pairs.size(), sc.data());
+  }
   if (st != OTGPU_OK) die("fill_dist_matrix", st, ctx);
   size_t q = 0, a = 0;
   for (size_t g = 0; g < jobs.size(); ++g) {
@@ -356,8 +366,10 @@ void invalid_reassignments(const bool& ignore_haps, const double& min_sim,
   }
   std::vector<int32_t> sc(pairs.size());
   if (!pairs.empty()) {
+    std::unique_lock<otb200::DeviceTurn> turn(otb200::device_turn(aligner.device()));
     int st = otgpu_edit_scores(ctx, S.bases, S.used, S.off.data(), S.len.data(),
                                (uint32_t)S.off.size(), pairs.data(), pairs.size(), sc.data());
+    turn.unlock();
     if (st != OTGPU_OK) die("invalid_reassignment", st, ctx);
   }
   // pass 2: the reference's loop (:131-176) on the live labels, scores looked up from pass 1

@@ -12,6 +12,7 @@
 
 #include "../csrc/exp_host_libm.cuh"
 #include "linkage_b200.hpp"
+#include "device_turn.hpp"
 #include "otter_b200.h"
 
 namespace {
@@ -175,9 +176,11 @@ void hclust_densities(const int& max_alleles, const double& bandwidth_short, con
     for (size_t k = a; k <= b; ++k) rel[k - a] = off[k] - off[a];
     std::vector<double> out((b - a) * grid.size());
     otgpu_ctx* ctx = aligner.context();
+    std::unique_lock<otb200::DeviceTurn> turn(otb200::device_turn(aligner.device()));
     const int st = ctx ? otgpu_kde_densities(ctx, values.data() + off[a], rel.data(), (uint32_t)(b - a),
                                              h.data() + a, grid.data(), (uint32_t)grid.size(), out.data())
                        : OTGPU_ERR_NO_DEVICE;
+    turn.unlock();
     if (st != OTGPU_OK) {
       std::cerr << "ERROR: otter_b200 density estimates: " << otgpu_strerror(st) << " ("
                 << (ctx ? otgpu_last_cuda_error(ctx) : "") << ")" << std::endl;

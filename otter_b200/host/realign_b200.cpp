@@ -12,6 +12,7 @@
 #include <cmath>
 
 #include "analignments_b200.hpp"
+#include "device_turn.hpp"
 #include "otter_b200.h"
 #include "ppoa_b200.hpp"
 
@@ -92,6 +93,7 @@ void batched_cigars(wfa::WFAligner& aligner2, const std::vector<CigarJob>& jobs,
   std::vector<int32_t> scores(jobs.size()), clen(jobs.size());
   const char* packed = nullptr;        // context-owned pinned memory, valid until the next call
   const uint64_t* begin = nullptr;
+  std::unique_lock<otb200::DeviceTurn> turn(otb200::device_turn(aligner2.device()));
   if (cigars) {  // the strings: packed on the device, only their bytes are copied back
     st = aligner2.isEdit()
         ? otgpu_edit_cigars_packed(ctx, bases, used, off.data(), len.data(), (uint32_t)order.size(),
@@ -108,6 +110,7 @@ void batched_cigars(wfa::WFAligner& aligner2, const std::vector<CigarJob>& jobs,
                               pairs.data(), pairs.size(), aligner2.mismatch(), aligner2.gapOpening(),
                               aligner2.gapExtension(), scores.data(), nullptr, nullptr, clen.data());
   }
+  turn.unlock();  // (the packed CIGARs sit in pinned memory this context owns until its next call)
   if (st != OTGPU_OK) die("batched_cigars", st, ctx);
   for (size_t i = 0; i < jobs.size(); ++i) {
     if (cigars && clen[i] >= 0) (*cigars)[i].assign(packed + begin[i], (size_t)clen[i]);

@@ -42,6 +42,7 @@ class WFAligner {
   // B200 additions (not in the reference): the device context behind this aligner, shared by
   // the batched entry points; which CUDA device new aligners bind to (default 0).
   otgpu_ctx* context() { return ctx_; }
+  int device() const { return device_; }
   bool isEdit() const { return kind_ == kEdit; }
   int mismatch() const { return x_; }
   int gapOpening() const { return o_; }
@@ -61,6 +62,7 @@ class WFAligner {
   AlignmentScope scope_;
   int x_, o_, e_;
   otgpu_ctx* ctx_ = nullptr;
+  int device_ = 0;
   int score_ = 0;
   int status_ = 0;
   std::string cigar_;

@@ -17,7 +17,8 @@ WFAligner::WFAligner(Kind kind, AlignmentScope scope, int mismatch, int gapOpeni
     : kind_(kind), scope_(scope), x_(mismatch), o_(gapOpening), e_(gapExtension) {
   // No device -> ctx_ stays null and every align call reports StatusDeviceError: there is no CPU
   // implementation to fall back to.
-  if (otgpu_create(g_default_device, &ctx_) != OTGPU_OK) ctx_ = nullptr;
+  device_ = g_default_device;
+  if (otgpu_create(device_, &ctx_) != OTGPU_OK) ctx_ = nullptr;
 }
 
 WFAligner::~WFAligner() { otgpu_destroy(ctx_); }
