@@ -45,8 +45,9 @@ struct DevBatch {
   uint32_t n_reads;
 };
 
-// counters[0] main queue, [1] wide (overflow) count, [2] wide queue, [3] 8-bit pairs
-struct Counters { unsigned long long v[4]; };
+// counters[0] main queue, [1] wide (overflow) count, [2] wide queue, [3] 8-bit pairs,
+// [4] pairs re-run on an HBM ring inside the main kernel
+struct Counters { unsigned long long v[8]; };
 
 __global__ void __launch_bounds__(128) k_pack_reads(DevBatch b, uint32_t* __restrict__ packed) {
   const uint32_t r = blockIdx.x;
@@ -149,12 +150,27 @@ __device__ __forceinline__ SeqView view8(const DevBatch& b, uint32_t r) {
   return SeqView{(uint32_t)(o >> 2), (int)(o & 3ull)};
 }
 
+// A pair whose wavefront outgrew the shared ring, started again on this warp's HBM ring without
+// leaving the kernel (out of line, so that the hot kernel's register allocation is its own).
+template <int BITS>
+__device__ __noinline__ int wfa_edit_pair_hbm(int32_t* ws, int mask, const EditJob J, const int lane) {
+  Ring<0> ring;
+  ring.p = ws;
+  ring.mask = mask;
+  return wfa_edit_pair<BITS, 0>(ring, J, lane);
+}
+
 #ifndef OTGPU_ALIGN_MIN_CTAS
 #define OTGPU_ALIGN_MIN_CTAS 4
 #endif
 // One pair per warp.  CAP > 0: pairs named by `list` (count in ctr->v[count_slot], or all
-// b.n_pairs of them when count_slot < 0), wavefront ring of CAP slots in shared memory; pairs that
-// outgrow it go to ovf_list.  CAP == 0 ("wide"): the pairs of ovf_list, ring in HBM.
+// b.n_pairs of them when count_slot < 0), wavefront ring of CAP slots in shared memory; a pair that
+// outgrows it goes to ovf_list — except on the 2048-slot tier (batches of long reads, where such
+// pairs actually occur), which starts the pair again at once on the warp's own HBM ring when the
+// launch has one per warp (wide_ws != nullptr): the heaviest pairs come first in the queue, so
+// their long single-warp runs overlap everything else instead of forming a tail.  (The call costs
+// the 64-register 1024-slot kernel spills and 10 % of its speed, so that tier keeps two passes.)
+// CAP == 0 ("wide"): the pairs of ovf_list, ring in HBM.
 // CAP = 1024 keeps 4 CTAs (32 warps) per SM; 2048 (3 CTAs) is for batches of long reads, whose
 // wavefronts pass a thousand diagonals.
 constexpr size_t ring_bytes(int cap) { return (size_t)(kWarpsPerCta + 1) * cap * 4; }
@@ -206,6 +222,13 @@ k_align(DevBatch b, Counters* __restrict__ ctr, const uint32_t* __restrict__ lis
       score = wfa_edit_pair<2, CAP>(ring, J, lane);
     }
     __syncwarp();
+    if (CAP == 2048 && score == kScoreOverflow && wide_ws != nullptr) {
+      int32_t* ws = wide_ws + (size_t)(blockIdx.x * kWarpsPerCta + warp) * wide_cap;
+      score = bytes ? wfa_edit_pair_hbm<8>(ws, wide_cap - 1, J, lane)
+                    : wfa_edit_pair_hbm<2>(ws, wide_cap - 1, J, lane);
+      if (lane == 0) atomicAdd(&ctr->v[4], 1ull);
+      __syncwarp();
+    }
     if (lane == 0) {
       if (!WIDE && score == kScoreOverflow) {
         const unsigned long long pos = atomicAdd(&ctr->v[1], 1ull);
@@ -253,6 +276,7 @@ struct otgpu_ctx {
   uint32_t n_reads = 0, n_regions = 0, max_len = 0;
   int grid_main = 0, grid_main_long = 0, grid_wide = 0, wide_cap = 0, wide_per_sm = 2;
   int force_ring = 0;  // OTGPU_RING_SLOTS=1024|2048 at otgpu_create: pin the ring tier (tests)
+  bool wide_two_pass = false;  // OTGPU_WIDE_TWO_PASS=1 at otgpu_create: always use k_align<0> (tests)
   // streaming of large region batches (otgpu_region_edit_scores): a second context on the same
   // device, made on first use, so that chunk i+1 uploads while chunk i aligns
   otgpu_ctx* peer = nullptr;
@@ -422,6 +446,7 @@ int otgpu_create(int device, otgpu_ctx** out) {
     const int v = atoi(rs);
     if (v == 1024 || v == 2048) ctx->force_ring = v;
   }
+  if (const char* tp = getenv("OTGPU_WIDE_TWO_PASS")) ctx->wide_two_pass = atoi(tp) != 0;
   if (const char* cm = getenv("OTGPU_CHUNK_MB")) {
     const long v = atol(cm);
     if (v > 0) ctx->chunk_bases = (uint64_t)v << 20;
@@ -613,10 +638,15 @@ int otgpu_batch_align(otgpu_ctx* ctx) {
     uint32_t* ovf = static_cast<uint32_t*>(ctx->ovf_list.p);
     uint32_t* order = static_cast<uint32_t*>(ctx->order.p);
     // wavefront width grows with read length: batches of long reads get the 2048-slot ring
-    if (ctx->force_ring ? ctx->force_ring == 2048 : ctx->max_len > kLongReadLen)
-      k_align<2048><<<ctx->grid_main_long, kCtaThreads, ring_bytes(2048), st>>>(b, ctr, order, -1, 0, ovf, nullptr, 0);
+    const bool long_ring = ctx->force_ring ? ctx->force_ring == 2048 : ctx->max_len > kLongReadLen;
+    const int grid = long_ring ? ctx->grid_main_long : ctx->grid_main;
+    // one HBM ring per warp of this launch (the wide workspace holds grid_wide CTAs' worth): pairs
+    // that outgrow the shared ring continue inside the kernel; else they wait for k_align<0>
+    int32_t* ws = grid <= ctx->grid_wide && !ctx->wide_two_pass ? static_cast<int32_t*>(ctx->wide_ws.p) : nullptr;
+    if (long_ring)
+      k_align<2048><<<grid, kCtaThreads, ring_bytes(2048), st>>>(b, ctr, order, -1, 0, ovf, ws, ctx->wide_cap);
     else
-      k_align<1024><<<ctx->grid_main, kCtaThreads, ring_bytes(1024), st>>>(b, ctr, order, -1, 0, ovf, nullptr, 0);
+      k_align<1024><<<grid, kCtaThreads, ring_bytes(1024), st>>>(b, ctr, order, -1, 0, ovf, ws, ctx->wide_cap);
     CK(cudaEventRecord(ctx->ev[3], st));
     k_align<0><<<ctx->grid_wide, kCtaThreads, 0, st>>>(
         b, ctr, ovf, 1, 2, ovf, static_cast<int32_t*>(ctx->wide_ws.p), ctx->wide_cap);
@@ -656,7 +686,7 @@ int otgpu_batch_download(otgpu_ctx* ctx, int32_t* scores_out, uint64_t n_scores)
   CK(cudaStreamSynchronize(ctx->stream));
   const Counters* hc = static_cast<const Counters*>(ctx->h_counters);
   ctx->stats.n_pairs = ctx->n_pairs;
-  ctx->stats.n_pairs_wide = hc->v[1];
+  ctx->stats.n_pairs_wide = hc->v[1] + hc->v[4];
   ctx->stats.n_pairs_8bit = hc->v[3];
   return OTGPU_OK;
 }

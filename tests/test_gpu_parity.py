@@ -98,6 +98,38 @@ def test_golden_pairs_through_c_abi(ctx, golden):
         del os.environ["OTGPU_RING_SLOTS"]
 
 
+def test_long_read_tier_finishes_wide_pairs_inside_the_kernel(built):
+    """Batches of long reads (2048-slot tier): a pair whose wavefront outgrows the shared ring is
+    started again on the warp's HBM ring inside k_align<2048>; OTGPU_WIDE_TWO_PASS=1 keeps the
+    older second kernel (k_align<0>).  Same scores either way, and equal to the oracle.
+    The two 45 kb regions hold pairs whose wavefronts reach ~2,500 diagonals (instrumented port)."""
+    import otter_b200
+    regions = [S.tr_region(np.random.default_rng(seed), 4, 45000, 0.05, extra_frac=0.1)
+               for seed in (26, 27)]
+    B = S.region_batch(regions)
+    out = {}
+    for two_pass in ("0", "1"):
+        os.environ["OTGPU_WIDE_TWO_PASS"] = two_pass
+        try:
+            with otter_b200.Context(0) as c:
+                out[two_pass] = c.region_edit_scores(B["bases"], B["off"], B["lens"], B["region_start"],
+                                                     B["score_off"], B["n_scores"])
+                assert c.stats()["n_pairs_wide"] > 0, "workload no longer reaches the HBM ring"
+        finally:
+            del os.environ["OTGPU_WIDE_TWO_PASS"]
+    assert np.array_equal(out["0"], out["1"])
+    P = S.port()
+    q = 0
+    for reads in regions:
+        for i in range(len(reads)):
+            for j in range(i + 1, len(reads)):
+                x, y = S.b(reads[i]), S.b(reads[j])
+                if len(x) < len(y):
+                    x, y = y, x
+                assert out["0"][q] == P.wfo_edit_score(x, len(x), y, len(y), 0, 0, 0, 0, 0, None), (q, i, j)
+                q += 1
+
+
 def test_golden_regions_through_region_abi(ctx, golden):
     regs = [g for g in golden["regions"] if all(s == 3 for s in g["span"])]
     B = S.region_batch([[u8(r) for r in g["reads"]] for g in regs])
