@@ -584,8 +584,14 @@ double ref_assemble_regions(const char* bases, const uint64_t* off, const uint32
               std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - a0).count());
     }
   };
+  // host-stage pool size: with two issuers the two host stages run at once next to two issuing
+  // threads, so each gets a share of the cores instead of all of them (OTREF_HOST_THREADS overrides)
+  int issuers = 1;
+  if (const char* e = getenv("OTREF_ISSUERS")) issuers = atoi(e);
+  int pool_threads = issuers >= 2 ? std::max(1, (threads - 2) / 2) : threads;
+  if (const char* e = getenv("OTREF_HOST_THREADS")) pool_threads = std::max(1, atoi(e));
   auto blocks = [&](uint32_t a, uint32_t b, auto&& f) {
-    parallel_blocks(b - a, threads, [&](uint32_t i) { f(a + i); });
+    parallel_blocks(b - a, pool_threads, [&](uint32_t i) { f(a + i); });
   };
   std::vector<ConsensusJob> cjobs(n_regions);  // one slot per region (unused when no valid read)
   std::vector<std::vector<double>> dens(n_regions);
@@ -669,8 +675,6 @@ double ref_assemble_regions(const char* bases, const uint64_t* off, const uint32
   };
   uint32_t wave = 100;
   if (const char* e = getenv("OTREF_WAVE")) wave = (uint32_t)atoi(e);
-  int issuers = 1;
-  if (const char* e = getenv("OTREF_ISSUERS")) issuers = atoi(e);
   otb200::run_waves(n_regions, wave, st, issuers);
 #endif
   return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
