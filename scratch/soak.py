@@ -15,9 +15,14 @@ ctx = ob.Context(0)
 vp = C.c_void_p
 regions = []
 for _ in range(int(sys.argv[2]) if len(sys.argv) > 2 else 400):
-    tl = int(rng.choice([20, 80, 300, 1000, 2500, 5000, 9000]))
-    e = float(rng.choice([0.0, 0.002, 0.01, 0.05, 0.12, 0.3]))
-    n = int(rng.integers(2, 26))
+    if os.environ.get("SOAK_LONG"):  # long-read tier: 2048-slot rings, pairs finished on HBM rings
+        tl = int(rng.choice([9000, 15000, 25000, 45000]))
+        e = float(rng.choice([0.005, 0.05, 0.08]))
+        n = int(rng.integers(2, 8))
+    else:
+        tl = int(rng.choice([20, 80, 300, 1000, 2500, 5000, 9000]))
+        e = float(rng.choice([0.0, 0.002, 0.01, 0.05, 0.12, 0.3]))
+        n = int(rng.integers(2, 26))
     reads = S.tr_region(rng, n, tl, e, extra_frac=float(rng.choice([0.0, 0.2, 0.6])), n_rate=float(rng.choice([0, 0, 0.1, 0.5])))
     if rng.random() < 0.1:
         reads[int(rng.integers(0, n))] = reads[0].copy()       # identical pair
