@@ -673,7 +673,11 @@ double ref_assemble_regions(const char* bases, const uint64_t* off, const uint32
       });
     });
   };
-  uint32_t wave = 100;
+  // wave size: the consensus alignments need a few hundred regions per launch before their
+  // persistent warps stop waiting for the longest alignment (profiles/README.md r1n: 34.5 ms per
+  // 100 regions in waves of 100, 18 ms per 100 in waves of 400), while four waves are enough to
+  // overlap the host stages
+  uint32_t wave = std::min(400u, std::max(100u, n_regions / 4));
   if (const char* e = getenv("OTREF_WAVE")) wave = (uint32_t)atoi(e);
   otb200::run_waves(n_regions, wave, st, issuers);
 #endif
