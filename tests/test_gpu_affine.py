@@ -253,3 +253,12 @@ def test_wave_of_regions_equals_reference(built):
     assert na[5] == 0 and max(na) == 2
     one = S.assemble_region(R, regions[0], spans[0])
     assert one["labels"] == la[0] and one["n_alleles"] == na[0]
+    # the same in five overlapped waves, device stages from one issuing thread and from two
+    # (wave_b200.hpp, device_turn.hpp): results depend on neither
+    for issuers in ("1", "2"):
+        os.environ["OTREF_WAVE"], os.environ["OTREF_ISSUERS"] = "5", issuers
+        try:
+            lc, nc, dc = S.assemble_regions(T, regions, spans, threads=4)
+        finally:
+            del os.environ["OTREF_WAVE"], os.environ["OTREF_ISSUERS"]
+        assert nc == na and lc == la and dc == da, issuers
