@@ -587,11 +587,36 @@ int otgpu_batch_upload_pairs(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_ba
   return OTGPU_OK;
 }
 
+#ifdef OTGPU_CHECK_BOUNDS
+// Checking build only (tests): tell the kernels which two buffers a window load may touch, and let
+// the test read back how many loads were checked and how many would have left them.
+static int check_set_ranges(otgpu_ctx* ctx) {
+  CheckRange r[2];
+  r[0].lo = static_cast<const uint32_t*>(ctx->packed.p);
+  r[0].hi = r[0].lo + ctx->packed.cap / 4;
+  r[1].lo = static_cast<const uint32_t*>(ctx->bases.p);
+  r[1].hi = r[1].lo + ctx->bases.cap / 4;
+  CK(cudaMemcpyToSymbolAsync(otgpu_check_range, r, sizeof r, 0, cudaMemcpyHostToDevice, ctx->stream));
+  return OTGPU_OK;
+}
+int otgpu_check_counts(otgpu_ctx* ctx, unsigned long long* loads, unsigned long long* oob) {
+  if (!ctx || !loads || !oob) return OTGPU_ERR_ARGS;
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaMemcpyFromSymbol(loads, otgpu_check_loads, sizeof *loads));
+  CK(cudaMemcpyFromSymbol(oob, otgpu_check_oob, sizeof *oob));
+  return OTGPU_OK;
+}
+#endif
+
 int otgpu_batch_align(otgpu_ctx* ctx) {
   if (!ctx) return OTGPU_ERR_ARGS;
   if (!ctx->resident) return OTGPU_ERR_STATE;
   CK(cudaSetDevice(ctx->device));
   cudaStream_t st = ctx->stream;
+#ifdef OTGPU_CHECK_BOUNDS
+  if (int cs = check_set_ranges(ctx)) return cs;
+#endif
   DevBatch b;
   b.bases = static_cast<const uint8_t*>(ctx->bases.p);
   b.read_off = static_cast<const uint64_t*>(ctx->read_off.p);
@@ -961,6 +986,9 @@ int cigars_impl(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const ui
   if (cig_bytes && !cigars_out && !packed) return OTGPU_ERR_ARGS;
   CK(cudaSetDevice(ctx->device));
   cudaStream_t st = ctx->stream;
+#ifdef OTGPU_CHECK_BOUNDS
+  if (int cs = check_set_ranges(ctx)) return cs;
+#endif
   // per-warp workspace: rings cover every diagonal of the longest pair, so they never alias
   const int wcap = next_pow2(2 * (int)ctx->max_len + 64);
   const uint32_t ops_cap = 4u * ctx->max_len + 64u;

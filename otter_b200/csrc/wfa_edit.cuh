@@ -100,6 +100,18 @@ struct Ring<0> {  // HBM workspace (L1/L2 cached), capacity covers every diagona
   }
 };
 
+// ---- checking build (-DOTGPU_CHECK_BOUNDS; tests only) ------------------------------------------
+// The window loads below are issued without guards (buffers carry guard regions instead, see
+// DESIGN.md §4).  The checking build verifies that claim from the inside: every window address is
+// compared with the two buffers it may fall into (the 2-bit copy, the raw bytes viewed as words),
+// a load that would leave them is counted and redirected to the start of the buffer.
+#ifdef OTGPU_CHECK_BOUNDS
+struct CheckRange { const uint32_t* lo; const uint32_t* hi; };
+__device__ CheckRange otgpu_check_range[2];
+__device__ unsigned long long otgpu_check_oob;
+__device__ unsigned long long otgpu_check_loads;
+#endif
+
 // ---- packed reads -----------------------------------------------------------------------------
 // A read as the kernel sees it: 32-bit word index of its first word inside the batch buffer
 // (2-bit words, or the raw byte buffer viewed as words) + position of base 0 inside that word.
@@ -132,6 +144,17 @@ __device__ __forceinline__ void window64(const uint32_t* __restrict__ words, con
   const uint32_t* q = words + wi;
 #else
   const uint32_t* q = words + (s.word0 + (uint32_t)(a >> Pack<BITS>::kLogBpw));
+#endif
+#ifdef OTGPU_CHECK_BOUNDS
+  {
+    const CheckRange r0 = otgpu_check_range[0], r1 = otgpu_check_range[1];
+    const bool ok = (q >= r0.lo && q + 3 <= r0.hi) || (q >= r1.lo && q + 3 <= r1.hi);
+    if (!ok) {
+      atomicAdd(&otgpu_check_oob, 1ull);
+      q = r0.lo;
+    }
+    if ((threadIdx.x & 31) == 0) atomicAdd(&otgpu_check_loads, 1ull);
+  }
 #endif
   const uint32_t w0 = __ldg(q), w1 = __ldg(q + 1), w2 = __ldg(q + 2);
   const int sh = a << Pack<BITS>::kLogBits;
