@@ -202,7 +202,7 @@ def work_counts(B, n_regions=2):
     class Counters(C.Structure):
         _fields_ = [("steps", C.c_int64), ("width_sum", C.c_int64), ("extend_bases", C.c_int64),
                     ("extend_words", C.c_int64), ("max_width", C.c_int32), ("cutoffs", C.c_int32),
-                    ("prunes", C.c_int32), ("pad_", C.c_int32), ("width_hist", C.c_int64 * 8),
+                    ("prunes", C.c_int32), ("prune_gate", C.c_int32), ("width_hist", C.c_int64 * 8),
                 ("run_hist", C.c_int64 * 8)]
     lib.wfo_edit_score.restype = C.c_int
     lib.wfo_edit_score.argtypes = [C.c_char_p, C.c_int, C.c_char_p, C.c_int] + [C.c_int] * 5 + [C.c_void_p]

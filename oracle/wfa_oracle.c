@@ -33,6 +33,7 @@ int wfo_edit_score(const char* pattern, int plen, const char* text, int tlen, in
   int32_t* Mn = bufB - kmin; /* next wavefront           */
   const int ak = tlen - plen; /* target diagonal, wavefront_extend.c:57 */
   int lo, hi, s = 0, k, result = -1;
+  int dm_ext = 0; /* minimum cut-off distance at the last extend (0 = unknown: the gate stays open) */
   if (ctr) memset(ctr, 0, sizeof(*ctr));
   for (k = kmin; k <= kmax; ++k) M[k] = Mn[k] = NUL;
   if (!endsfree) { /* wavefront_align.c:113-135 */
@@ -91,6 +92,7 @@ int wfo_edit_score(const char* pattern, int plen, const char* text, int tlen, in
       int dmin = imax(plen, tlen), nlo, nhi, top, bot; /* :230 */
 #define DIST(kk) (M[kk] >= 0 ? imax(plen - (M[kk] - (kk)), tlen - M[kk]) : -NUL) /* :111-119 */
       for (k = lo; k <= hi; ++k) dmin = imin(dmin, DIST(k));
+      dm_ext = dmin;
       top = imin(ak, hi); /* :269 */
       nlo = lo;
       for (k = lo; k < top; ++k) {
@@ -110,6 +112,12 @@ int wfo_edit_score(const char* pattern, int plen, const char* text, int tlen, in
     }
     /* ---- compute s+1 (wavefront_compute_edit.c:294-356, kernel :70-97) ---- */
     ++s;
+    /* The kernel's gate for splitting a step around the prune (wfa_edit.cuh, wfa_edit_run): a
+     * NECESSARY condition for the prune below to change anything, from the wavefront before this
+     * compute.  Counted so that tests can check "prune fired => gate was open". */
+    const int gate = !endsfree && hi - lo + 3 >= WFO_PRUNE_LEN &&
+                     imax(abs(lo - 1 - ak), abs(hi + 1 - ak)) >= dm_ext - 1;
+    if (ctr && gate) ctr->prune_gate++;
     {
       const int nlo = lo - 1, nhi = hi + 1;
       for (k = nlo; k <= nhi; ++k) {
@@ -142,6 +150,7 @@ int wfo_edit_score(const char* pattern, int plen, const char* text, int tlen, in
         if (!(BEST(lo) <= smax && BEST(hi) <= smax)) {
           int w = 0x7fffffff, nlo = lo, nhi = hi;
           if (ctr) ctr->prunes++;
+          if (ctr && !gate) ctr->prune_gate = -(1 << 30); /* would disprove the gate */
           for (k = lo; k <= hi; ++k)
             if (M[k] >= 0 && WORST(k) < w) w = WORST(k);
           for (k = lo; k <= hi; ++k) {

@@ -29,7 +29,8 @@ typedef struct {
   int32_t max_width;    /* widest wavefront seen at extend time                        */
   int32_t cutoffs;      /* steps on which the adaptive cut-off shrank the wavefront    */
   int32_t prunes;       /* exact-prune triggers (width >= 1000)                        */
-  int32_t pad_;
+  int32_t prune_gate;   /* steps on which the kernel's necessary condition for a prune held
+                           (negative: a prune fired with the gate closed - never)           */
   int64_t width_hist[8]; /* score steps by live width: <=30, <=61, <=125, <=189, <=253, <=509,
                             <=1021, wider (the kernel's narrow / mid / 2, 3, 4, 8, 16 rounds)   */
   int64_t run_hist[8];   /* extensions by matched bases: <31, <62, <93, <124, <248, <1116, <4000, more */

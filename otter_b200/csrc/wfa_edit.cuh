@@ -342,6 +342,7 @@ __device__ __forceinline__ int bitsel(int m, int a, int b) {
 struct WfState {
   int lo, hi;  // live diagonal range
   int dmin;    // per-lane partial minimum of the cut-off distance
+  int dm;      // warp-uniform minimum of the cut-off distance after the last extend
   bool fin;    // per-lane: ends-free termination met on a diagonal this lane owns
 };
 
@@ -568,6 +569,7 @@ __device__ __forceinline__ int wf_edges(const Ring<CAP>& R, const int plen, cons
     hi = S.hi;
   }
   const int dm = __reduce_min_sync(g.mask, S.dmin);
+  S.dm = dm;
   if (EF ? __any_sync(g.mask, S.fin) : (dm == 0)) return 1;
   if (hi - lo + 1 >= kMinWfLen) {
     const int dmin = min(max(plen, tlen), dm);  // :230-237
@@ -639,6 +641,7 @@ __device__ __forceinline__ int wf_step_narrow(const Ring<CAP>& R, const EditJob&
   int lo = clo + __ffs(b) - 1, hi = clo + 31 - __clz(b);
   // ---- termination (wavefront_extend.c:45-68, 122-168) ----
   const int dm = __reduce_min_sync(g.mask, dist);
+  S.dm = dm;
   if (EF ? __any_sync(g.mask, fin) : (dm == 0)) return 1;
   // ---- WF-adaptive cut-off (wavefront_heuristic.c:285-328) ----
   if (hi - lo + 1 >= kMinWfLen) {
@@ -701,9 +704,10 @@ __device__ __forceinline__ bool wf_prune(const Ring<CAP>& R, const int plen, con
 // (-2, never when WIDE).
 template <int BITS, int CAP, bool EF>
 __device__ int wfa_edit_run(const Ring<CAP>& R, const EditJob& J, const int lane) {
-  const int plen = J.plen, tlen = J.tlen;
+  const int plen = J.plen, tlen = J.tlen, ak = tlen - plen;
   const int cap = R.cap();
   WfState S;
+  S.dm = 0;
   int s = 0;
 
   const Grp<32> g(lane);
@@ -733,8 +737,16 @@ __device__ int wfa_edit_run(const Ring<CAP>& R, const EditJob& J, const int lane
     }
     // the pass touches slots [lo-2, hi+1+127] and relies on nulls outside [lo,hi]: no aliasing
     if (CAP != 0 && S.hi - S.lo + 136 > cap) return kScoreOverflow;
-    if (CAP == 0 && !EF && S.hi - S.lo + 3 >= kPruneLen) {
-      // the exact prune sits between compute and extend: run them as separate passes
+    // Exact prune (wavefront_compute_edit.c:214-269, call site :341-347), on every ring that can
+    // hold 1000 diagonals.  It sits between compute and extend, which the fused pass cannot
+    // separate, so the step is split only when the prune could do anything.  It acts iff
+    // |lo'-ak| or |hi'-ak| (best case of an edge diagonal of the trimmed wavefront [lo',hi'],
+    // inside [lo-1,hi+1]) exceeds the worst case max(plen-v, tlen-h) of the middle diagonal.
+    // Every offset of wavefront s+1 is at most one past a neighbouring offset of wavefront s, so
+    // that worst case is >= (minimum cut-off distance of wavefront s) - 1 = S.dm - 1: when both
+    // edge bounds stay below it the reference's prune returns at :234 and the fused step is exact.
+    if ((CAP == 0 || CAP >= kPruneLen + 136) && !EF && S.hi - S.lo + 3 >= kPruneLen &&
+        max(abs(S.lo - 1 - ak), abs(S.hi + 1 - ak)) >= S.dm - 1) {
       wf_pass<BITS, CAP, EF, true, false>(R, J, g, C, S);
       if (!wf_trim<CAP>(R, g, S)) return -1;
       if (!wf_prune<CAP>(R, plen, tlen, lane, S)) return -1;
