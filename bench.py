@@ -30,7 +30,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-from otter_b200 import synth  # noqa: E402
+from harness import synth  # noqa: E402
 
 METRIC = "read-pair alignments/sec"
 UNIT = "pairs/s"
@@ -536,8 +536,8 @@ def run_pipeline(args, rank, world, local_rank):
     """Integration measurement: assemble_process's loop body (src/assemble.cpp:103-142: distance
     matrix -> otter_hclust -> re-assignment -> rapid_consensus) over a wave of regions, host reads
     in, alleles out.  `ours` = the unmodified reference clustering / partial-order-consensus
-    objects linked on the product's host layer (oracle/_ref/libotter_intree.so, built by
-    oracle/Makefile from /root/reference + otter_b200/host): every alignment runs batched on the
+    objects linked on the product's host layer (integration/_build/libotter_intree.so, built by
+    integration/Makefile from /root/reference + otter_b200/host): every alignment runs batched on the
     GPU, everything else on the host threads.  `reference` = the unmodified reference
     (libotter_ref.so), one region at a time per host thread.  Both return per-region labels and
     allele digests; the ours arm checks them against the reference on a sample."""
@@ -550,7 +550,8 @@ def run_pipeline(args, rank, world, local_rank):
     vp = C.c_void_p
 
     def bind(name):
-        lib = C.CDLL(os.path.join(ROOT, "oracle", "_ref", name))
+        where = ("integration", "_build") if "intree" in name else ("oracle", "_ref")
+        lib = C.CDLL(os.path.join(ROOT, *where, name))
         lib.ref_assemble_regions.restype = C.c_double
         lib.ref_assemble_regions.argtypes = [vp, vp, vp, vp, vp, C.c_uint32, C.c_int, C.c_int, vp, vp, vp]
         return lib

@@ -122,6 +122,29 @@ int otgpu_region_edit_scores(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_ba
                              const uint64_t* read_off, const uint32_t* read_len,
                              uint32_t n_reads, const uint32_t* region_start, uint32_t n_regions,
                              const uint64_t* score_off, uint64_t n_scores, int32_t* scores_out);
+/* The same call for a caller that is still filling `bases` (and wants the scores as they come):
+ * the batch is cut into chunks of consecutive regions (about 64 MB of reads each; layout as above,
+ * region after region) and the chunks alternate between two sets of device buffers, so the
+ * caller's staging copy of chunk i+1 and its use of chunk i-1's scores overlap the kernels of
+ * chunk i.  Replaces the per-region loop body's call into fill_dist_matrix
+ * (src/assemble.cpp:103-110 -> src/analignments.cpp:117-124) when one host thread feeds a device.
+ *   wait_bases(user, upto)        called before the library first reads bases[0..upto): return
+ *                                  once those bytes are in place (the read, region and score
+ *                                  tables must be complete when the call is made);
+ *   scores_ready(user, first, n)   called once scores_out[first..first+n) are final.
+ * Either hook may be NULL.  Hooks run on the calling thread.  Scores are identical to
+ * otgpu_region_edit_scores. */
+typedef struct otgpu_stream_hooks {
+  void (*wait_bases)(void* user, uint64_t upto_byte);
+  void (*scores_ready)(void* user, uint64_t first_score, uint64_t n_scores);
+  void* user;
+} otgpu_stream_hooks;
+int otgpu_region_edit_scores_hooked(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                                    const uint64_t* read_off, const uint32_t* read_len,
+                                    uint32_t n_reads, const uint32_t* region_start,
+                                    uint32_t n_regions, const uint64_t* score_off,
+                                    uint64_t n_scores, int32_t* scores_out,
+                                    const otgpu_stream_hooks* hooks);
 /* Batches larger than ~1.5 x 256 MB of reads (laid out region after region, as above) are streamed
  * through two sets of device buffers in chunks of consecutive regions, so that the upload of one
  * chunk overlaps the alignment of the previous one and device memory stays bounded; scores are

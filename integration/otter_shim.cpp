@@ -1,22 +1,18 @@
-// oracle/ref_shim.cpp — TEST INFRASTRUCTURE ONLY.
+// integration/otter_shim.cpp — HARNESS, not product: one set of extern "C" entry points over
+// otter's own call surface, so that tests and bench.py can drive the same calls in two builds.
 //
-// Thin extern "C" shim over the UNMODIFIED reference (otter + vendored WFA2-lib v2.2), compiled
-// against the reference headers where they lie under /root/reference by oracle/Makefile into
-// oracle/_ref/libotter_ref.so.  Nothing here re-implements an algorithm: every entry point
-// constructs the reference's own objects (wfa::WFAlignerEdit / wfa::WFAlignerGapAffine, ANREAD,
-// DistMatrix) exactly the way src/assemble.cpp:49-50 does and calls the reference function.
-//
-// Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
-// load this library.  The product (otter_b200/) never does.
-// Built twice by oracle/Makefile:
-//   _ref/libotter_ref.so     against WFA2-lib's own WFAligner.hpp + the reference analignments.cpp
-//                            (the pure reference: oracle and CPU baseline);
-//   _ref/libotter_intree.so  -DOTTER_B200_IN_TREE: the same reference pipeline objects
-//                            (otterclust, ankde, anppoa, anseqs, hclust-cpp) but with
-//                            otter_b200/host/{analignments,realign,wfaligner}_b200.cpp in place of
-//                            analignments.cpp + WFA2, i.e. otter running on the GPU hot path.
-//                            Used by the GPU tests to compare whole-region results (labels,
-//                            alleles) with libotter_ref.so.
+// Nothing here re-implements an algorithm: every entry point constructs otter's own objects
+// (wfa::WFAlignerEdit / wfa::WFAlignerGapAffine, ANREAD, DistMatrix) exactly the way
+// src/assemble.cpp:49-50 does and calls the function of that name.  Built twice:
+//   oracle/_ref/libotter_ref.so             (oracle/Makefile) against the UNMODIFIED reference:
+//       WFA2-lib's own WFAligner.hpp + src/analignments.cpp - the oracle and the CPU baseline.
+//       Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
+//       load it; the product (otter_b200/) never does.
+//   integration/_build/libotter_intree.so   (integration/Makefile) -DOTTER_B200_IN_TREE: the same
+//       reference pipeline objects (otterclust, ankde, anppoa, anseqs, hclust-cpp) with
+//       otter_b200/host/{analignments,realign,wfaligner,otterclust}_b200.cpp in place of
+//       analignments.cpp + WFA2, i.e. otter running on the GPU hot path.  The GPU tests compare
+//       whole-region results (labels, alleles) between the two libraries.
 #include "bindings/cpp/WFAligner.hpp"
 #ifdef OTTER_B200_IN_TREE
 #include "analignments_b200.hpp"

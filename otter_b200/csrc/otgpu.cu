@@ -281,6 +281,7 @@ struct otgpu_ctx {
   // device, made on first use, so that chunk i+1 uploads while chunk i aligns
   otgpu_ctx* peer = nullptr;
   uint64_t chunk_bases = (uint64_t)256 << 20;  // OTGPU_CHUNK_MB at otgpu_create (tests use 1)
+  uint64_t hook_chunk_bases = (uint64_t)64 << 20;  // chunk size of the hooked call (OTGPU_CHUNK_MB too)
   uint64_t n_chunks_last = 0;
   otgpu_stats stats = {0, 0, 0, 0};
   cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // pack|expand|align|wide|end
@@ -449,7 +450,7 @@ int otgpu_create(int device, otgpu_ctx** out) {
   if (const char* tp = getenv("OTGPU_WIDE_TWO_PASS")) ctx->wide_two_pass = atoi(tp) != 0;
   if (const char* cm = getenv("OTGPU_CHUNK_MB")) {
     const long v = atol(cm);
-    if (v > 0) ctx->chunk_bases = (uint64_t)v << 20;
+    if (v > 0) ctx->chunk_bases = ctx->hook_chunk_bases = (uint64_t)v << 20;
   }
   cudaError_t e = cudaSetDevice(device);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
@@ -734,7 +735,8 @@ int otgpu_edit_scores(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
 static int region_scores_streamed(otgpu_ctx* ctx, const uint8_t* bases, const uint64_t* read_off,
                                   const uint32_t* read_len, const uint32_t* region_start,
                                   uint32_t n_regions, const uint64_t* score_off,
-                                  int32_t* scores_out) {
+                                  int32_t* scores_out, uint64_t chunk_bases,
+                                  const otgpu_stream_hooks* hooks) {
   if (!ctx->peer) {
     const int s = otgpu_create(ctx->device, &ctx->peer);
     if (s != OTGPU_OK) return s;
@@ -749,6 +751,7 @@ static int region_scores_streamed(otgpu_ctx* ctx, const uint8_t* bases, const ui
     if (!pend[k].on) return OTGPU_OK;
     pend[k].on = false;
     const int s = otgpu_batch_download(slot[k], scores_out + pend[k].s0, pend[k].ns);
+    if (s == OTGPU_OK && hooks && hooks->scores_ready) hooks->scores_ready(hooks->user, pend[k].s0, pend[k].ns);
     pairs_total += slot[k]->stats.n_pairs;
     wide_total += slot[k]->stats.n_pairs_wide;
     b8_total += slot[k]->stats.n_pairs_8bit;
@@ -758,9 +761,10 @@ static int region_scores_streamed(otgpu_ctx* ctx, const uint8_t* bases, const ui
   uint32_t g0 = 0;
   while (g0 < n_regions) {
     uint32_t g1 = g0;
-    const uint64_t base0 = read_off[region_start[g0]];
+    // (trailing regions without reads: region_start[g0] == n_reads, nothing left to address)
+    const uint64_t base0 = region_start[g0] < region_start[n_regions] ? read_off[region_start[g0]] : 0;
     uint64_t bytes = 0;
-    while (g1 < n_regions && (g1 == g0 || bytes < ctx->chunk_bases)) {
+    while (g1 < n_regions && (g1 == g0 || bytes < chunk_bases || region_start[g1] == region_start[n_regions])) {
       const uint32_t ra = region_start[g1], rb = region_start[g1 + 1];
       if (rb > ra) bytes = read_off[rb - 1] + read_len[rb - 1] - base0;
       ++g1;
@@ -781,6 +785,7 @@ static int region_scores_streamed(otgpu_ctx* ctx, const uint8_t* bases, const ui
     rs_c[g1 - g0] = r1 - r0;
     const int k = (int)(chunks & 1);
     int s = finish(k);  // the chunk before last on this slot: its buffers are about to be reused
+    if (hooks && hooks->wait_bases) hooks->wait_bases(hooks->user, base0 + bytes);
     if (s == OTGPU_OK)
       s = otgpu_batch_upload_regions(slot[k], bases + base0, bytes, off_c.data(), read_len + r0, r1 - r0,
                                      rs_c.data(), g1 - g0, so_c.data(), ns);
@@ -804,36 +809,60 @@ static int region_scores_streamed(otgpu_ctx* ctx, const uint8_t* bases, const ui
   return s;
 }
 
-int otgpu_region_edit_scores(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
-                             const uint64_t* read_off, const uint32_t* read_len,
-                             uint32_t n_reads, const uint32_t* region_start, uint32_t n_regions,
-                             const uint64_t* score_off, uint64_t n_scores, int32_t* scores_out) {
-  if (ctx) ctx->n_chunks_last = 1;
-  if (ctx && bases && read_off && read_len && region_start && score_off && scores_out &&
-      n_regions > 1 && n_bases > ctx->chunk_bases + ctx->chunk_bases / 2) {
-    // streaming needs reads and scores laid out region after region, which is how every caller
-    // here builds them; verify, else fall through to the single batch
-    bool ok = region_start[0] == 0 && region_start[n_regions] == n_reads && score_off[0] == 0;
-    uint64_t at = 0, sc = 0;
-    for (uint32_t g = 0; ok && g < n_regions; ++g) {
-      if (region_start[g + 1] < region_start[g] || region_start[g + 1] > n_reads) { ok = false; break; }
-      const uint64_t n = region_start[g + 1] - region_start[g];
-      ok = score_off[g] == sc;
-      sc += n * (n ? n - 1 : 0) / 2;
-      for (uint32_t r = region_start[g]; ok && r < region_start[g + 1]; ++r) {
-        ok = read_off[r] >= at && read_off[r] + read_len[r] <= n_bases;
-        at = read_off[r] + read_len[r];
-      }
+// Layout check of the streamed path: reads and scores of consecutive regions are consecutive.
+static bool regions_are_consecutive(const uint64_t* read_off, const uint32_t* read_len, uint32_t n_reads,
+                                    uint64_t n_bases, const uint32_t* region_start, uint32_t n_regions,
+                                    const uint64_t* score_off, uint64_t n_scores) {
+  bool ok = region_start[0] == 0 && region_start[n_regions] == n_reads && score_off[0] == 0;
+  uint64_t at = 0, sc = 0;
+  for (uint32_t g = 0; ok && g < n_regions; ++g) {
+    if (region_start[g + 1] < region_start[g] || region_start[g + 1] > n_reads) return false;
+    const uint64_t n = region_start[g + 1] - region_start[g];
+    ok = score_off[g] == sc;
+    sc += n * (n ? n - 1 : 0) / 2;
+    for (uint32_t r = region_start[g]; ok && r < region_start[g + 1]; ++r) {
+      ok = read_off[r] >= at && read_off[r] + read_len[r] <= n_bases;
+      at = read_off[r] + read_len[r];
     }
-    if (ok && sc == n_scores)
-      return region_scores_streamed(ctx, bases, read_off, read_len, region_start, n_regions, score_off,
-                                    scores_out);
   }
+  return ok && sc == n_scores;
+}
+
+int otgpu_region_edit_scores_hooked(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                                    const uint64_t* read_off, const uint32_t* read_len,
+                                    uint32_t n_reads, const uint32_t* region_start,
+                                    uint32_t n_regions, const uint64_t* score_off,
+                                    uint64_t n_scores, int32_t* scores_out,
+                                    const otgpu_stream_hooks* hooks) {
+  if (ctx) ctx->n_chunks_last = 1;
+  const bool hooked = hooks && (hooks->wait_bases || hooks->scores_ready);
+  // with hooks the chunks are smaller: their purpose is overlap with the caller's own work
+  const uint64_t chunk = hooked ? (ctx ? ctx->hook_chunk_bases : 0) : (ctx ? ctx->chunk_bases : 0);
+  if (ctx && bases && read_off && read_len && region_start && score_off && scores_out &&
+      n_regions > 1 && n_bases > chunk + chunk / 2) {
+    // streaming needs reads and scores laid out region after region, which is how every caller
+    // here builds them; verify (the tables only - the bases may still be on their way), else fall
+    // through to the single batch
+    if (regions_are_consecutive(read_off, read_len, n_reads, n_bases, region_start, n_regions, score_off,
+                                n_scores))
+      return region_scores_streamed(ctx, bases, read_off, read_len, region_start, n_regions, score_off,
+                                    scores_out, chunk, hooked ? hooks : nullptr);
+  }
+  if (hooked && hooks->wait_bases) hooks->wait_bases(hooks->user, n_bases);
   int s = otgpu_batch_upload_regions(ctx, bases, n_bases, read_off, read_len, n_reads,
                                      region_start, n_regions, score_off, n_scores);
   if (s == OTGPU_OK) s = otgpu_batch_align(ctx);
   if (s == OTGPU_OK) s = otgpu_batch_download(ctx, scores_out, n_scores);
+  if (s == OTGPU_OK && hooked && hooks->scores_ready) hooks->scores_ready(hooks->user, 0, n_scores);
   return s;
+}
+
+int otgpu_region_edit_scores(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                             const uint64_t* read_off, const uint32_t* read_len,
+                             uint32_t n_reads, const uint32_t* region_start, uint32_t n_regions,
+                             const uint64_t* score_off, uint64_t n_scores, int32_t* scores_out) {
+  return otgpu_region_edit_scores_hooked(ctx, bases, n_bases, read_off, read_len, n_reads, region_start,
+                                         n_regions, score_off, n_scores, scores_out, nullptr);
 }
 
 }  // extern "C"

@@ -604,69 +604,89 @@ __device__ __forceinline__ int wf_edges(const Ring<CAP>& R, const int plen, cons
   return 0;
 }
 
-// One whole score step for a NARROW wavefront: the computed range [lo-1,hi+1] fits one lane per
-// diagonal, so compute, extend, trim, termination and cut-off all work on registers — one ring
-// load and one store per lane, no probes, no round loop.  Low-error reads (HiFi) spend most of
-// their steps here.  Same order of operations and return value as wf_pass + wf_edges.
-template <int BITS, int CAP, bool EF, int G>
-__device__ __forceinline__ int wf_step_narrow(const Ring<CAP>& R, const EditJob& J, const Grp<G>& g,
-                                              const LaneConst& C, WfState& S) {
+// Consecutive score steps of a NARROW wavefront, held in registers: lane L owns diagonal kb + L
+// for as long as the computed range [lo-1,hi+1] stays inside lanes 1..30 (lanes 0 and 31 are
+// always null, so the neighbour shuffles need no edge masks); the window is re-centred when the
+// range drifts to an edge.  No ring traffic, no __syncwarp: compute, extend, trim, termination and
+// cut-off of a step are ~80 instructions.  Low-error reads (HiFi) spend most of their steps here.
+// The ring is all nulls while the wavefront lives in registers; it is written back on the way out.
+// Same order of operations as wf_pass + wf_edges.  Returns 1 = alignment done, -1 = wavefront
+// empty, 0 = the next step needs more than 30 lanes (wavefront [S.lo,S.hi] is back in the ring).
+template <int BITS, int CAP, bool EF>
+__device__ __forceinline__ int wf_narrow_run(const Ring<CAP>& R, const EditJob& J, const int lane,
+                                             WfState& S, int& s) {
   constexpr int WE = Pack<BITS>::kWin - 1;
   const int plen = J.plen, tlen = J.tlen, ak = tlen - plen;
-  const int clo = S.lo - 1;  // S.hi + 1 - clo + 1 <= G
-  const int k = clo + g.gl;
-  const int cur = R.ld(k);  // null outside [lo,hi]
-  // ---- compute (wavefront_compute_edit.c:70-97) ----
-  const int left = bitsel(C.mk0, kENull, __shfl_up_sync(g.mask, cur, 1));
-  const int right = bitsel(C.mk31, kENull, __shfl_down_sync(g.mask, cur, 1));
-  int m = max(right, max(left, cur) + 1);
-  const int v = m - k, pr = plen - v, tr = tlen - m, rem = min(pr, tr);
-  const bool ok = (m | v | rem) >= 0;
-  // ---- extend (wavefront_extend.c:203-260) ----
-  int n = (int)min(first_diff<BITS>(J, v, m), (uint32_t)rem);
-  if (__any_sync(g.mask, n == WE)) {
-    const bool c = ok && n == WE && rem > WE;
-    if (__any_sync(g.mask, c)) n = lcp_more<BITS, G>(J, g, v, m, rem, c, n);
-  }
-  m += n;
-  bool fin = false;
-  if (EF) fin = ok && ((tr - n <= 0 && pr - n <= J.pe) || (pr - n <= 0 && tr - n <= J.te));
-  const int sv = ok ? m : kENull;
-  const int dist = plen + max(k, ak) - sv;  // cut-off distance; in the millions for a null
-  R.st(k, sv);
-  __syncwarp(g.mask);
-  // ---- trim (wavefront_compute.c:376-409) ----
-  const unsigned b = __ballot_sync(g.mask, sv >= 0) >> g.first;
-  if (b == 0) return -1;
-  int lo = clo + __ffs(b) - 1, hi = clo + 31 - __clz(b);
-  // ---- termination (wavefront_extend.c:45-68, 122-168) ----
-  const int dm = __reduce_min_sync(g.mask, dist);
-  S.dm = dm;
-  if (EF ? __any_sync(g.mask, fin) : (dm == 0)) return 1;
-  // ---- WF-adaptive cut-off (wavefront_heuristic.c:285-328) ----
-  if (hi - lo + 1 >= kMinWfLen) {
-    const int dmin = min(max(plen, tlen), dm);
-    const bool keep = dist - dmin <= kMaxDist;
-    const int top = min(ak, hi);
-    int nlo = lo;
-    if (lo < top) {
-      const unsigned b2 = __ballot_sync(g.mask, k >= lo && k < top && keep) >> g.first;
-      nlo = b2 ? clo + __ffs(b2) - 1 : top;
+  const int dcap = max(plen, tlen);
+  int lo = S.lo, hi = S.hi;
+  // centre the computed range [lo-1,hi+1] (<= 30 wide) in lanes 1..30
+  int kb = lo - 2 - ((28 - (hi - lo)) >> 1);
+  int k = kb + lane;
+  int m = R.ld(k);        // nulls outside [lo,hi] (ring invariant)
+  R.st(k, kENull);        // the ring holds nothing while the wavefront is in registers
+  int kdist = plen + max(k, ak);  // cut-off distance of an offset on diagonal k = kdist - offset
+  int dm = S.dm;
+  int st;
+  for (;;) {
+    ++s;
+    // ---- compute (wavefront_compute_edit.c:70-97) ----
+    const int left = __shfl_up_sync(kFull, m, 1), right = __shfl_down_sync(kFull, m, 1);
+    m = max(right, max(left, m) + 1);
+    const int v = m - k, pr = plen - v, tr = tlen - m, rem = min(pr, tr);
+    const bool ok = (m | v | rem) >= 0;
+    // ---- extend (wavefront_extend.c:203-260) ----
+    int n = (int)min(first_diff<BITS>(J, v, m), (uint32_t)rem);
+    if (__any_sync(kFull, n == WE)) {
+      const bool c = ok && n == WE && rem > WE;
+      if (__any_sync(kFull, c)) n = lcp_more<BITS, 32>(J, Grp<32>(lane), v, m, rem, c, n);
     }
-    const int bot = max(ak, nlo);
-    int nhi = hi;
-    if (hi > bot) {
-      const unsigned b3 = __ballot_sync(g.mask, k <= hi && k > bot && keep) >> g.first;
-      nhi = b3 ? clo + 31 - __clz(b3) : bot;
+    bool fin = false;
+    if (EF) fin = ok && ((tr - n <= 0 && pr - n <= J.pe) || (pr - n <= 0 && tr - n <= J.te));
+    m = ok ? m + n : kENull;
+    const int dist = kdist - m;  // in the millions for a null
+    // ---- trim, termination, cut-off: three votes back to back, then straight-line lane-mask
+    // arithmetic (wavefront_compute.c:376-409; wavefront_extend.c:45-68,122-168;
+    // wavefront_heuristic.c:285-328) ----
+    const unsigned okb = __ballot_sync(kFull, ok);
+    dm = __reduce_min_sync(kFull, dist);
+    const bool done = EF ? __any_sync(kFull, fin) : (dm == 0);
+    const unsigned keepb = __ballot_sync(kFull, dist <= min(dcap, dm) + kMaxDist);  // :230-237
+    if (okb == 0) { st = -1; break; }
+    if (done) { st = 1; break; }
+    int llo = __clz(__brev(okb)), lhi = 31 - __clz(okb);  // trim: first / last in-bounds diagonal
+    // cut-off only from kMinWfLen diagonals on: below that every live diagonal is kept
+    const unsigned kp = (lhi - llo + 1 >= kMinWfLen) ? keepb : okb;
+    const int first = __clz(__brev(kp)), last = 31 - __clz(kp);  // kp != 0: the minimum is kept
+    const int lak = ak - kb;  // lane of the target diagonal (may lie outside 0..31)
+    // lo: first kept diagonal below top = min(ak, hi), else top; untouched when lo >= top (:269-275)
+    const int nlo = max(llo, min(first, min(lak, lhi)));
+    // hi: last kept diagonal above bot = max(ak, lo'), else bot; untouched when hi <= bot (:277-283)
+    const int nhi = min(lhi, max(last, max(lak, nlo)));
+    if ((unsigned)(lane - nlo) > (unsigned)(nhi - nlo)) m = kENull;
+    llo = nlo;
+    lhi = nhi;
+    lo = kb + llo;
+    hi = kb + lhi;
+    // ---- room for the next step's range [lo-1,hi+1] in lanes 1..30? ----
+    if (llo < 2 || lhi > 29) {
+      if (lhi - llo > 27) { st = 0; break; }
+      const int nkb = lo - 2 - ((28 - (hi - lo)) >> 1);
+      const int src = lane + (nkb - kb);
+      const int mv = __shfl_sync(kFull, m, src & 31);
+      m = (unsigned)src < 32u ? mv : kENull;
+      kb = nkb;
+      k = kb + lane;
+      kdist = plen + max(k, ak);
     }
-    if ((k >= lo && k < nlo) || (k <= hi && k > nhi)) R.st(k, kENull);  // ring invariant
-    __syncwarp(g.mask);
-    lo = nlo;
-    hi = nhi;
   }
   S.lo = lo;
   S.hi = hi;
-  return 0;
+  S.dm = dm;
+  if (st == 0) {
+    R.st(k, m);
+    __syncwarp();
+  }
+  return st;
 }
 
 // Exact prune, end-to-end only, width >= 1000 (wavefront_compute_edit.c:214-269).
@@ -730,11 +750,11 @@ __device__ int wfa_edit_run(const Ring<CAP>& R, const EditJob& J, const int lane
   int st = wf_edges<CAP, EF>(R, plen, tlen, g, S.lo, S.hi, S);
 
   while (st == 0) {
-    ++s;
-    if (S.hi - S.lo + 3 <= 32) {
-      st = wf_step_narrow<BITS, CAP, EF>(R, J, g, C, S);
+    if (S.hi - S.lo + 3 <= 30) {  // the computed range fits lanes 1..30: register-resident steps
+      st = wf_narrow_run<BITS, CAP, EF>(R, J, lane, S, s);
       continue;
     }
+    ++s;
     // the pass touches slots [lo-2, hi+1+127] and relies on nulls outside [lo,hi]: no aliasing
     if (CAP != 0 && S.hi - S.lo + 136 > cap) return kScoreOverflow;
     // Exact prune (wavefront_compute_edit.c:214-269, call site :341-347), on every ring that can

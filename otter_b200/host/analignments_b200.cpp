@@ -6,10 +6,15 @@
 #include "analignments_b200.hpp"
 
 #include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
 #include <cstdint>
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
+#include <map>
+#include <memory>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -80,10 +85,27 @@ struct Staging {
   }
 };
 
-Staging& staging() {
-  thread_local Staging s;
-  return s;
+// One staging area per device context (an aligner owns its context and is used by one thread at
+// a time, like the reference's per-thread aligners): the pinned buffer is allocated once and
+// re-used by every later call on that aligner, whichever host thread makes it.
+Staging& staging(otgpu_ctx* ctx) {
+  static std::mutex m;
+  static std::map<otgpu_ctx*, std::unique_ptr<Staging>> by_ctx;
+  std::lock_guard<std::mutex> lk(m);
+  auto& p = by_ctx[ctx];
+  if (!p) p.reset(new Staging());
+  return *p;
 }
+
+double now_s() {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+thread_local FillTimes g_last_fill = {0, 0, 0, 0, 0};
+
+// Producer side of the hooked C-ABI call: worker threads copy the reads into the pinned staging
+// buffer front to back and publish how far they got; the library waits for the bytes of a chunk
+// right before it uploads them, and hands back each chunk's scores as soon as they are final, so
+// the copy of chunk i+1 and the conversion of chunk i-1's scores run under the kernels of chunk i.
 
 }  // namespace
 
@@ -148,9 +170,14 @@ std::vector<int> partition_regions_by_work(const std::vector<RegionDistJob>& job
 }
 
 void fill_dist_matrices_multi(const bool& ignore_haps, std::vector<wfa::WFAligner*>& aligners,
-                              std::vector<RegionDistJob>& jobs) {
+                              std::vector<RegionDistJob>& jobs, std::vector<FillTimes>* times) {
   if (aligners.empty()) die("fill_dist_matrices_multi", OTGPU_ERR_ARGS, nullptr);
-  if (aligners.size() == 1 || !ignore_haps) return fill_dist_matrices(ignore_haps, *aligners[0], jobs);
+  if (times) times->assign(aligners.size(), FillTimes{0, 0, 0, 0, 0});
+  if (aligners.size() == 1 || !ignore_haps) {
+    fill_dist_matrices(ignore_haps, *aligners[0], jobs);
+    if (times) (*times)[0] = last_fill_times();
+    return;
+  }
   for (auto* a : aligners)
     if (!a || !a->context()) die("fill_dist_matrices_multi", OTGPU_ERR_NO_DEVICE, nullptr);
   const std::vector<int> part = partition_regions_by_work(jobs, (int)aligners.size());
@@ -160,8 +187,14 @@ void fill_dist_matrices_multi(const bool& ignore_haps, std::vector<wfa::WFAligne
   std::vector<std::thread> pool;
   for (size_t d = 1; d < aligners.size(); ++d)
     if (!share[d].empty())
-      pool.emplace_back([&, d] { fill_dist_matrices(ignore_haps, *aligners[d], share[d]); });
-  if (!share[0].empty()) fill_dist_matrices(ignore_haps, *aligners[0], share[0]);
+      pool.emplace_back([&, d] {
+        fill_dist_matrices(ignore_haps, *aligners[d], share[d]);
+        if (times) (*times)[d] = last_fill_times();
+      });
+  if (!share[0].empty()) {
+    fill_dist_matrices(ignore_haps, *aligners[0], share[0]);
+    if (times) (*times)[0] = last_fill_times();
+  }
   for (auto& th : pool) th.join();
 }
 
@@ -179,7 +212,7 @@ void fill_dist_matrices(const bool& ignore_haps, wfa::WFAligner& aligner,
   }
   otgpu_ctx* ctx = aligner.context();
   if (!ctx) die("fill_dist_matrix", OTGPU_ERR_NO_DEVICE, nullptr);
-  Staging& S = staging();
+  Staging& S = staging(ctx);
   size_t total = 0;
   bool all_spanning = true;
   for (auto& J : jobs)
@@ -206,48 +239,112 @@ void fill_dist_matrices(const bool& ignore_haps, wfa::WFAligner& aligner,
     const uint64_t n = jobs[g].indeces->size();
     n_scores += n * (n ? n - 1 : 0) / 2;
   }
-  {  // the copy into pinned staging is the longest host step of a wave: a few threads share it
-    const int workers = total > ((size_t)8 << 20) ? 4 : 1;
-    auto copy = [&](size_t a, size_t b) {
-      for (size_t r = a; r < b; ++r) std::memcpy(S.bases + S.off[r], seqs[r]->data(), seqs[r]->size());
-    };
-    std::vector<std::thread> pool;
-    const size_t per = (seqs.size() + workers - 1) / workers;
-    for (int t = 1; t < workers; ++t)
-      if ((size_t)t * per < seqs.size()) pool.emplace_back(copy, (size_t)t * per, std::min(seqs.size(), (size_t)(t + 1) * per));
-    copy(0, std::min(seqs.size(), per));
-    for (auto& th : pool) th.join();
-  }
+  const double t_begin = now_s();
+  // The copy into pinned staging is the longest host step of a wave.  Worker threads run it front
+  // to back and publish a watermark; in the all-spanning case (below) the device call starts at
+  // once and waits, chunk by chunk, only for the bytes it is about to upload.
+  const int workers = total > ((size_t)8 << 20) ? 4 : 1;
+  const size_t n_seqs = seqs.size();
+  constexpr size_t kBlock = 64;  // reads per unit of work
+  const size_t n_blocks = (n_seqs + kBlock - 1) / kBlock;
+  std::vector<std::atomic<uint8_t>> block_done(n_blocks);
+  for (auto& d : block_done) d.store(0, std::memory_order_relaxed);
+  std::atomic<size_t> next_block{0};
+  auto copy = [&](int) {  // blocks are taken in order, so the buffer fills front to back
+    for (;;) {
+      const size_t b = next_block.fetch_add(1, std::memory_order_relaxed);
+      if (b >= n_blocks) return;
+      const size_t r1 = std::min(n_seqs, (b + 1) * kBlock);
+      for (size_t r = b * kBlock; r < r1; ++r) std::memcpy(S.bases + S.off[r], seqs[r]->data(), seqs[r]->size());
+      block_done[b].store(1, std::memory_order_release);
+    }
+  };
+  double stage_wait_s = 0.0;
+  size_t blocks_seen = 0;  // every block below this one is known to be complete
+  auto wait_reads = [&](size_t upto_read) {  // returns once reads [0, upto_read) are in place
+    const size_t need = std::min(n_blocks, (upto_read + kBlock - 1) / kBlock);
+    if (blocks_seen >= need) return;
+    const double t0 = now_s();
+    for (; blocks_seen < need; ++blocks_seen)
+      while (!block_done[blocks_seen].load(std::memory_order_acquire)) std::this_thread::yield();
+    stage_wait_s += now_s() - t0;
+  };
+  std::vector<std::thread> pool;
+  for (int t = 1; t < workers; ++t) pool.emplace_back(copy, t);
+  struct Joiner {
+    std::vector<std::thread>& p;
+    ~Joiner() { for (auto& th : p) if (th.joinable()) th.join(); }
+  } joiner{pool};
   std::vector<int32_t> scores(n_scores);
   if (all_spanning) {
     // every pair is alignEnd2End(longer, shorter): pairs are expanded on the device
+    double unpack_s = 0.0;
+    // scores [first, first+n) are final: form the dissimilarities of the regions they belong to
+    size_t g_next = 0;
+    auto unpack = [&](uint64_t first, uint64_t n) {
+      const double t0 = now_s();
+      const uint64_t end = first + n;
+      for (; g_next < jobs.size(); ++g_next) {
+        const size_t g = g_next;
+        const uint64_t cnt = jobs[g].indeces->size();
+        if (score_off[g] + cnt * (cnt ? cnt - 1 : 0) / 2 > end) break;
+        auto& idx = *jobs[g].indeces;
+        auto& reads = *jobs[g].reads;
+        const int32_t* sc = scores.data() + score_off[g];
+        // (i,j) in this order is the order of the condensed store itself (src/andistmat.cpp:15-21),
+        // so element q is written directly instead of through set_dist's index arithmetic
+        double* out = jobs[g].distmatrix->values.data();
+        size_t q = 0;
+        for (uint32_t i = 0; i < idx.size(); ++i)
+          for (uint32_t j = i + 1; j < idx.size(); ++j, ++q) {
+            const size_t lx = reads[idx[i]].seq.size(), ly = reads[idx[j]].seq.size();
+            const double largest = lx < ly ? (double)ly : (double)lx;  // :68
+            // equal strings score 0, and 0/largest == 0.0 == the :64 shortcut
+            out[q] = sc[q] / largest;                                  // :71-72
+          }
+      }
+      unpack_s += now_s() - t0;
+    };
+    struct Hooks {
+      decltype(wait_reads)* wait;
+      decltype(unpack)* done;
+      const Staging* S;
+      size_t cursor;  // first read whose end lies beyond the last byte asked for
+    } H{&wait_reads, &unpack, &S, 0};
+    otgpu_stream_hooks hooks;
+    hooks.user = &H;
+    hooks.wait_bases = [](void* u, uint64_t upto) {
+      Hooks* h = static_cast<Hooks*>(u);
+      while (h->cursor < h->S->off.size() && h->S->off[h->cursor] < upto) ++h->cursor;
+      (*h->wait)(h->cursor);
+    };
+    hooks.scores_ready = [](void* u, uint64_t first, uint64_t n) {
+      Hooks* h = static_cast<Hooks*>(u);
+      (*h->done)(first, n);
+    };
     int st;
+    double t_dev0, t_dev1;
+    // a small batch is copied inline; a large one by the helpers while this thread drives the device
+    if (workers == 1) copy(0);
+    else pool.emplace_back(copy, 0);
     {
       std::lock_guard<otb200::DeviceTurn> turn(otb200::device_turn(aligner.device()));
-      st = otgpu_region_edit_scores(ctx, S.bases, S.used, S.off.data(), S.len.data(),
-                                    (uint32_t)S.off.size(), region_start.data(),
-                                    (uint32_t)jobs.size(), score_off.data(), n_scores,
-                                    scores.data());
+      t_dev0 = now_s();
+      st = otgpu_region_edit_scores_hooked(ctx, S.bases, S.used, S.off.data(), S.len.data(),
+                                           (uint32_t)S.off.size(), region_start.data(),
+                                           (uint32_t)jobs.size(), score_off.data(), n_scores,
+                                           scores.data(), &hooks);
+      t_dev1 = now_s();
     }
     if (st != OTGPU_OK) die("fill_dist_matrix", st, ctx);
-    for (size_t g = 0; g < jobs.size(); ++g) {
-      auto& idx = *jobs[g].indeces;
-      auto& reads = *jobs[g].reads;
-      const int32_t* sc = scores.data() + score_off[g];
-      // (i,j) in this order is the order of the condensed store itself (src/andistmat.cpp:15-21),
-      // so element q is written directly instead of through set_dist's index arithmetic
-      double* out = jobs[g].distmatrix->values.data();
-      size_t q = 0;
-      for (uint32_t i = 0; i < idx.size(); ++i)
-        for (uint32_t j = i + 1; j < idx.size(); ++j, ++q) {
-          const size_t lx = reads[idx[i]].seq.size(), ly = reads[idx[j]].seq.size();
-          const double largest = lx < ly ? (double)ly : (double)lx;  // :68
-          // equal strings score 0, and 0/largest == 0.0 == the :64 shortcut
-          out[q] = sc[q] / largest;                                  // :71-72
-        }
-    }
+    unpack(n_scores, 0);  // regions without pairs at the tail
+    const double t_end = now_s();
+    g_last_fill = FillTimes{t_end - t_begin, t_dev1 - t_dev0, stage_wait_s, unpack_s,
+                            (double)otgpu_last_chunk_count(ctx)};
     return;
   }
+  copy(0);
+  wait_reads(n_seqs);
   // general case: some valid reads are not spanning -> per-pair plan, explicit pair list
   std::vector<otgpu_pair> pairs;
   std::vector<PairPlan> plans;
@@ -313,7 +410,7 @@ void invalid_reassignments(const bool& ignore_haps, const double& min_sim,
   (void)ignore_haps;  // the reference always aligns here: get_dist_anreads(true, ...) (:144)
   otgpu_ctx* ctx = aligner.context();
   if (!ctx) die("invalid_reassignment", OTGPU_ERR_NO_DEVICE, nullptr);
-  Staging& S = staging();
+  Staging& S = staging(ctx);
   size_t total = 0;
   for (auto& J : jobs)
     for (auto& r : *J.reads) total += r.seq.size();
@@ -417,3 +514,5 @@ void invalid_reassignments(const bool& ignore_haps, const double& min_sim,
     }
   }
 }
+
+FillTimes last_fill_times() { return g_last_fill; }

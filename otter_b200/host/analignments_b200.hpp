@@ -32,6 +32,13 @@ struct RegionDistJob {
 void fill_dist_matrices(const bool& ignore_haps, wfa::WFAligner& aligner,
                         std::vector<RegionDistJob>& jobs);
 
+// Where the time of this thread's last all-spanning fill_dist_matrices call went (seconds): the
+// whole call, the device call inside it (uploads, kernels, downloads, and the waits below), the
+// part of the device call spent waiting for the staging copy, the score -> dissimilarity
+// conversion (runs under the kernels of later chunks), and the number of chunks.
+struct FillTimes { double total_s, device_call_s, stage_wait_s, unpack_s, chunks; };
+FillTimes last_fill_times();
+
 // The same over several devices of one box from ONE host process: `aligners`
 // holds one WFAlignerEdit per device (WFAligner::setDefaultDevice(d) before constructing it).
 // Regions are independent, so the jobs are partitioned across the aligners by estimated work
@@ -40,7 +47,8 @@ void fill_dist_matrices(const bool& ignore_haps, wfa::WFAligner& aligner,
 // place: the gather is the host memory the caller already owns, there is no collective.  Results
 // do not depend on the partition.
 void fill_dist_matrices_multi(const bool& ignore_haps, std::vector<wfa::WFAligner*>& aligners,
-                              std::vector<RegionDistJob>& jobs);
+                              std::vector<RegionDistJob>& jobs,
+                              std::vector<FillTimes>* times = nullptr);  // times: one per aligner
 // Which aligner each job goes to (exposed for tests): loads[] receives the per-aligner estimate.
 std::vector<int> partition_regions_by_work(const std::vector<RegionDistJob>& jobs, int n_parts,
                                            std::vector<double>* loads = nullptr);

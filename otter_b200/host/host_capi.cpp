@@ -1,6 +1,8 @@
 // otter_b200/host/host_capi.cpp — flat extern "C" entry points over the C++ host layer so the
 // Python parity tests (ctypes) can drive the reference-shaped C++ functions
 // (fill_dist_matrix, invalid_reassignment, align_anreads) exactly as otter would.
+#include <algorithm>
+#include <chrono>
 #include <cstdint>
 #include <cstring>
 #include <memory>
@@ -108,6 +110,54 @@ void othost_fill_dist_matrices_multi(const char* bases, const uint64_t* off, con
     for (uint32_t g = 0; g < n_regions; ++g) part_out[g] = part[g];
   }
   fill_dist_matrices_multi(true, aligners, jobs);
+  for (uint32_t g = 0; g < n_regions; ++g)
+    if (!dms[g].values.empty())
+      std::memcpy(out + out_off[g], dms[g].values.data(), dms[g].values.size() * sizeof(double));
+}
+
+// Timed runs of the seam otter calls: fill_dist_matrices (n_devices == 1) or
+// fill_dist_matrices_multi over `devices`, from std::string-shaped reads that exist before the
+// clock starts (as otter's ANREADs do), `warmup` untimed calls first.  times_out holds 6 doubles
+// per timed call: wall seconds of the call, then max over the devices of {whole share, device
+// call, wait for the staging copy inside it, score -> dissimilarity conversion}, then the number
+// of chunks of device 0.  `out` receives the last call's matrices.
+void othost_bench_fill(const char* bases, const uint64_t* off, const uint32_t* len,
+                       const uint32_t* region_start, uint32_t n_regions, const int* devices,
+                       int n_devices, int warmup, int reps, double* out, const uint64_t* out_off,
+                       double* times_out) {
+  std::vector<std::vector<ANREAD>> reads(n_regions);
+  std::vector<std::vector<int>> idx(n_regions);
+  std::vector<DistMatrix> dms;
+  dms.reserve(n_regions);
+  std::vector<RegionDistJob> jobs;
+  for (uint32_t g = 0; g < n_regions; ++g) {
+    reads[g] = build_reads(bases, off, len, nullptr, region_start[g], region_start[g + 1]);
+    idx[g].resize(reads[g].size());
+    for (size_t i = 0; i < idx[g].size(); ++i) idx[g][i] = (int)i;
+    dms.emplace_back((uint32_t)reads[g].size());
+  }
+  for (uint32_t g = 0; g < n_regions; ++g) jobs.push_back({&reads[g], &idx[g], &dms[g]});
+  std::vector<std::unique_ptr<wfa::WFAlignerEdit>> own;
+  std::vector<wfa::WFAligner*> aligners;
+  for (int a = 0; a < n_devices; ++a) {
+    wfa::WFAligner::setDefaultDevice(devices[a]);
+    own.emplace_back(new wfa::WFAlignerEdit(wfa::WFAligner::Score, wfa::WFAligner::MemoryMed));
+    aligners.push_back(own.back().get());
+  }
+  wfa::WFAligner::setDefaultDevice(0);
+  std::vector<FillTimes> times;
+  for (int r = 0; r < warmup + reps; ++r) {
+    const auto t0 = std::chrono::steady_clock::now();
+    fill_dist_matrices_multi(true, aligners, jobs, &times);
+    const double wall = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (r < warmup) continue;
+    double* t = times_out + 6 * (size_t)(r - warmup);
+    t[0] = wall; t[1] = t[2] = t[3] = t[4] = 0.0; t[5] = times[0].chunks;
+    for (const FillTimes& f : times) {
+      t[1] = std::max(t[1], f.total_s); t[2] = std::max(t[2], f.device_call_s);
+      t[3] = std::max(t[3], f.stage_wait_s); t[4] = std::max(t[4], f.unpack_s);
+    }
+  }
   for (uint32_t g = 0; g < n_regions; ++g)
     if (!dms[g].values.empty())
       std::memcpy(out + out_off[g], dms[g].values.data(), dms[g].values.size() * sizeof(double));

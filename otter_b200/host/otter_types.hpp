@@ -95,4 +95,15 @@ class DistMatrix {
   }
   uint32_t size() const { return (uint32_t)values.size(); }
 };
+// src/otterclust.hpp:7-14 (what otter_hclust fills)
+class ClusteringStatus {
+ public:
+  int ic;
+  int fc;
+  std::vector<int> labels;
+  ClusteringStatus() : ic(0), fc(0) {}
+  void set_global_label(int l) {
+    for (uint32_t i = 0; i < labels.size(); ++i) labels[i] = l;
+  }
+};
 #endif

@@ -1,5 +1,4 @@
 // otter_b200/host/otterclust_b200.cpp — see otterclust_b200.hpp.
-#ifdef OTTER_B200_IN_TREE
 #include "otterclust_b200.hpp"
 
 #include <algorithm>
@@ -300,4 +299,3 @@ void otter_hclust_batch(const bool& ignore_haps, const int& max_alleles, const d
   }
   for (auto& th : pool) th.join();
 }
-#endif  // OTTER_B200_IN_TREE

@@ -7,14 +7,16 @@
 // normalisation, maxima / minima, the decision bound, average-linkage clustering and the tree
 // cuts (linkage_b200.hpp, bit-identical to hclust-cpp's hclust_fast / cutree_cdist / cutree_k),
 // the coverage-based relabelling — runs per region on the host in the reference's order of
-// operations.  In-tree only: it needs otter's ClusteringStatus (src/otterclust.hpp:7-14).
+// operations.  ClusteringStatus is otter's own (src/otterclust.hpp:7-14) in the in-tree build and
+// its mirror in otter_types.hpp stand-alone.
 #pragma once
-#ifdef OTTER_B200_IN_TREE
 #include <vector>
 
 #include "bindings/cpp/WFAligner.hpp"
 #include "otter_types.hpp"
+#ifdef OTTER_B200_IN_TREE
 #include "otterclust.hpp"
+#endif
 
 struct HclustJob {
   const std::vector<int>* indeces;   // valid (spanning) reads
@@ -41,4 +43,3 @@ void hclust_densities(const int& max_alleles, const double& bandwidth_short, con
 void hclust_finish(const int& max_alleles, const double& max_tolerable_diff, const double& min_cov_fraction,
                    const int& min_cov_fraction2_l, const double& min_cov_fraction2_f, HclustJob& job,
                    std::vector<double>& densities, double bandwidth);
-#endif

@@ -16,7 +16,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 PORT_SO = os.path.join(ROOT, "oracle", "libwfa_oracle.so")
 REF_SO = os.path.join(ROOT, "oracle", "_ref", "libotter_ref.so")
-INTREE_SO = os.path.join(ROOT, "oracle", "_ref", "libotter_intree.so")
+INTREE_SO = os.path.join(ROOT, "integration", "_build", "libotter_intree.so")
 
 c_char_p, c_int, c_u32, c_u64, c_dbl = C.c_char_p, C.c_int, C.c_uint32, C.c_uint64, C.c_double
 vp = C.c_void_p
@@ -123,7 +123,7 @@ def intree():
 
 
 def assemble_region(lib, reads, span, max_alleles=2):
-    """Run one region through src/assemble.cpp:103-142 (via ref_shim) -> dict."""
+    """Run one region through src/assemble.cpp:103-142 (via integration/otter_shim.cpp) -> dict."""
     bases, off, lens = pack_reads(reads)
     n = len(reads)
     sp = np.array(span, dtype=np.uint8)
@@ -162,7 +162,7 @@ def assemble_regions(lib, regions, spans, max_alleles=2, threads=4):
     return [labels[rs[g]:rs[g + 1]].tolist() for g in range(len(regions))], n_al.tolist(), dig.tolist()
 
 
-from otter_b200.synth import (ALPHA, rand_seq, mutate, tr_region, pack_reads,  # noqa: E402,F401
+from harness.synth import (ALPHA, rand_seq, mutate, tr_region, pack_reads,  # noqa: E402,F401
                                region_batch, make_regions, pair_lengths)
 
 

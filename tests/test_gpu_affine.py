@@ -168,7 +168,7 @@ def test_golden_local_realignment(built, agold):
     assert trimmed > 0
 
 
-@pytest.mark.skipif(not S.have_intree(), reason="oracle/_ref/libotter_intree.so is prebuilt in the build container")
+@pytest.mark.skipif(not S.have_intree(), reason="integration/_build/libotter_intree.so is prebuilt in the build container")
 def test_whole_regions_equal_reference_golden(built, agold):
     """fill_dist_matrix -> otter_hclust -> invalid_reassignment -> rapid_consensus with the
     reference's own clustering/consensus code on top of the GPU hot path: labels, alleles,
@@ -179,7 +179,7 @@ def test_whole_regions_equal_reference_golden(built, agold):
         assert res == g["result"]
 
 
-@pytest.mark.skipif(not S.have_intree(), reason="oracle/_ref/libotter_intree.so is prebuilt in the build container")
+@pytest.mark.skipif(not S.have_intree(), reason="integration/_build/libotter_intree.so is prebuilt in the build container")
 def test_ppoa_known_answers_on_gpu_cigars(built, agold):
     """test/ppoa_test.cpp's expected consensus strings, with the CIGARs coming from the GPU."""
     T = S.intree()

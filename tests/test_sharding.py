@@ -13,7 +13,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 import support as S  # noqa: E402
-from otter_b200 import sharding  # noqa: E402
+from harness import sharding  # noqa: E402
 
 
 def make_batch():
