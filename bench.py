@@ -9,13 +9,22 @@ alignment (WFA, WF-adaptive heuristic, bit-exact to the reference) for the named
             kernels), CUDA events on the library's stream, max over ranks.
   e2e       pairs/s through the C-ABI call a host would make (otgpu_region_edit_scores) with
             PINNED HOST buffers: H2D of reads + kernels + D2H of scores inside the timed region.
-  roofline  dominant kernel k_align<1024> (k_align<2048> for long-read batches): algorithmic bytes (2-bit reads once per pair + 4 B
-            score) / its CUDA-event duration, against MEASURED_PEAKS.json hbm_gbs.
-  cpu_baseline  the reference's own fill_dist_matrix (oracle/_ref) — or our C port when the
-            reference library is absent — on all host threads, on a bounded sample of the workload.
-N>1: one process per GPU (torchrun), each rank aligns its own seeded batch of the same shape
-(weak scaling; regions are independent, no data-path collective); value = pairs of all ranks /
-max-over-ranks time.
+  e2e_host_layer  the same through the C++ seam otter itself calls (fill_dist_matrices from
+            per-read std::strings): staging copy and score conversion included.
+  roofline  dominant kernel k_align<1024> (k_align<2048> for long-read batches): algorithmic bytes
+            (2-bit reads once per pair + 4 B score) / its CUDA-event duration, against
+            MEASURED_PEAKS.json hbm_gbs; issue_slots only from an ncu capture of THIS csrc tree.
+  cpu_baseline  the reference's own fill_dist_matrix (oracle/_ref) on all host threads over >= 20
+            regions per thread, and identical_to_reference: the GPU scores of those regions,
+            as dissimilarities, against its doubles bit for bit.
+  per_config    (N=1) the same measurement for C1, C3 and one eighth of the 100 k-region description.
+  c4_strong     north_star's target: ONE 100 k-region HiFi description partitioned by estimated
+            work over the ranks, each rank's pass + a host-side gather on rank 0; with N>1 rank 0
+            also runs the whole description alone, so speedup_vs_n1 comes from one run.
+  single_process  (N>1, rank 0) one host process feeding all N devices (fill_dist_matrices_multi).
+N>1 headline: one process per GPU (torchrun), each rank aligns its own seeded batch of the same
+shape (weak scaling; regions are independent, no data-path collective); value = pairs of all
+ranks / max-over-ranks time.
 """
 import argparse
 import json
@@ -36,36 +45,17 @@ METRIC = "read-pair alignments/sec"
 UNIT = "pairs/s"
 
 
-def load_traffic(workload, n_regions):
-    """DRAM bytes per launch of the dominant kernel from the committed ncu capture (same workload)."""
-    p = os.path.join(ROOT, "profiles", "r1f_traffic.json")
-    if workload == "C2" and n_regions == synth.CONFIGS["C2"]["n_regions"] and os.path.exists(p):
-        try:
-            return json.load(open(p))["traffic_bytes_per_launch"]
-        except Exception:
-            pass
-    return None
-
-
-def load_warp_instructions(workload, n_regions):
-    """Warp instructions per launch of the dominant kernel from the same committed ncu capture."""
-    p = os.path.join(ROOT, "profiles", "r1f_traffic.json")
-    if workload == "C2" and n_regions == synth.CONFIGS["C2"]["n_regions"] and os.path.exists(p):
-        try:
-            return json.load(open(p)).get("warp_instructions")
-        except Exception:
-            pass
-    return None
-
-
 def load_peaks():
+    """HBM peak for the roofline: the driver-measured STREAM-style copy of MEASURED_PEAKS.json, else
+    the fallback /opt/skills/guides/B200_PROFILING.md states (6.65 TB/s, an earlier measurement on
+    this pool)."""
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         try:
-            return json.load(open(p)).get("hbm_gbs", 6650.0), "measured"
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
         except Exception:
             pass
-    return 6650.0, "fallback"
+    return 6650.0, "fallback (B200_PROFILING.md: 6.65 TB/s)"
 
 
 class ClockSampler:
@@ -242,39 +232,6 @@ def work_counts(B, n_regions=2):
                                         "wider"), hist)),
             "extensions_by_matched_bases": dict(zip(("lt31", "lt62", "lt93", "lt124", "lt248", "lt1116",
                                                      "lt4000", "more"), runs))}
-
-
-def run_reference(args, rank, world):
-    if rank != 0:
-        return
-    B = workload_arrays(args.workload, 0, args.regions)
-    base, run, R = cpu_reference(B, 4.0)
-    for _ in range(max(args.warmup, 0)):
-        run(min(R, max(8, R // 4)))
-    tot_p, tot_t = 0, 0.0
-    for _ in range(args.steps):
-        n_sc, t = run(R)
-        tot_p += n_sc
-        tot_t += t
-    v = tot_p / tot_t
-    base.update(value=v)
-    base.pop("pairs"), base.pop("seconds")
-    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32",
-            "data": "synthetic", "config": config_dict(args, B, world),
-            "cpu_baseline": base,
-            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
-
-
-def config_dict(args, B, world):
-    c = synth.CONFIGS[args.workload]
-    return {"workload": f"{args.workload}: {c['desc']}", "regions_per_gpu": B["n_regions"],
-            "reads_per_region": c["n_reads"], "pairs_per_gpu": B["n_scores"],
-            "bases_per_gpu": int(B["bases"].size), "parallelism": f"region-sharded x{world}",
-            "l2_policy": "inputs_exceed_l2" if B["bases"].size > 126e6 else "l2_flushed_between_steps"}
 
 
 def consensus_requests(B):
@@ -603,6 +560,427 @@ def run_pipeline(args, rank, world, local_rank):
     print(json.dumps(line), flush=True)
 
 
+def csrc_sha():
+    """Hash of the kernel sources: ncu-derived constants (traffic, warp instructions) are only
+    quoted when they were captured on this very tree."""
+    import hashlib
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "otter_b200", "csrc")
+    for f in sorted(os.listdir(d)):
+        if f.endswith((".cu", ".cuh", ".inc")):
+            h.update(f.encode())
+            h.update(open(os.path.join(d, f), "rb").read())
+    return h.hexdigest()[:16]
+
+
+def load_capture(workload, n_regions):
+    """The committed ncu capture of the dominant kernel for this workload (profiles/*_traffic.json:
+    DRAM bytes and warp instructions per launch), or (None, reason)."""
+    best = None
+    for f in sorted(os.listdir(os.path.join(ROOT, "profiles"))):
+        if f.endswith("_traffic.json"):
+            try:
+                j = json.load(open(os.path.join(ROOT, "profiles", f)))
+            except Exception:
+                continue
+            if j.get("workload") == workload and j.get("n_regions") == n_regions:
+                best = (f, j)
+    if best is None:
+        return None, "no capture of this workload"
+    f, j = best
+    if j.get("csrc_sha") != csrc_sha():
+        return None, f"stale capture (profiles/{f} was taken on csrc {j.get('csrc_sha')}, this tree is {csrc_sha()})"
+    j["file"] = f
+    return j, None
+
+
+def reference_doubles(B, R, threads=None):
+    """The unmodified reference's dissimilarities of the first R regions (oracle/_ref), or None."""
+    import ctypes as C
+    ref_so = os.path.join(ROOT, "oracle", "_ref", "libotter_ref.so")
+    if not os.path.exists(ref_so) or R < 1:
+        return None, 0.0
+    lib = C.CDLL(ref_so)
+    lib.ref_fill_dist_matrix_regions.restype = C.c_double
+    vp = C.c_void_p
+    lib.ref_fill_dist_matrix_regions.argtypes = [vp, vp, vp, vp, C.c_uint32, vp, vp, C.c_int]
+    rs, so = B["region_start"], B["score_off"]
+    n_sc = int(so[R - 1] + (rs[R] - rs[R - 1]) * (rs[R] - rs[R - 1] - 1) // 2)
+    out = np.empty(n_sc, dtype=np.float64)
+    p = lambda a: a.ctypes.data_as(vp)  # noqa: E731
+    t = lib.ref_fill_dist_matrix_regions(p(B["bases"]), p(B["off"]), p(B["lens"]), p(rs), R, p(out), p(so),
+                                         threads or os.cpu_count() or 1)
+    return out, t
+
+
+def scores_to_doubles(B, scores, n_sc):
+    """score / (double)largest, as fill_dist_matrix forms it (src/analignments.cpp:68-72)."""
+    lens = B["lens"].astype(np.float64)
+    rs = B["region_start"]
+    out = np.empty(n_sc, dtype=np.float64)
+    q = 0
+    g = 0
+    while q < n_sc:
+        L = lens[rs[g]:rs[g + 1]]
+        i, j = np.triu_indices(len(L), 1)
+        k = len(i)
+        out[q:q + k] = scores[q:q + k] / np.maximum(L[i], L[j])
+        q += k
+        g += 1
+    return out
+
+
+def cpu_baseline_leg(B, scores, regions_per_thread=20, min_seconds=8.0):
+    """The reference's fill_dist_matrix on all host threads over the first R regions, R >= 20 per
+    thread (static contiguous blocks: fewer and the slowest block sets the number), and the check
+    of the GPU scores of those regions against its doubles."""
+    threads = os.cpu_count() or 1
+    n_regions = B["n_regions"]
+    base, run, _ = cpu_reference(B, 2.0, threads)           # short probe: rate of this workload
+    R = min(n_regions, regions_per_thread * threads)
+    pairs_per_region = max(B["n_scores"] / max(n_regions, 1), 1.0)
+    R = int(min(n_regions, max(R, base["value"] * min_seconds / pairs_per_region)))
+    R = max(1, R - R % threads) if R >= threads else R
+    want, t = reference_doubles(B, R, threads)
+    if want is not None and t < 4.0:  # a short sample is noisy: the reference keeps its better pass
+        t = min(t, reference_doubles(B, R, threads)[1])
+    if want is None:                                          # reference library absent: the C port
+        n_sc, t = run(R)
+        return dict(value=n_sc / t, unit=UNIT, cores=threads, kind=base["kind"],
+                    sample=f"first {R} of {n_regions} regions ({n_sc} pairs) in {t:.2f} s; " + base["sample"].split("; ", 1)[1]), None
+    n_sc = len(want)
+    same = None
+    if scores is not None:
+        mine = scores_to_doubles(B, scores, n_sc)
+        same = bool(np.array_equal(mine.view(np.uint64), want.view(np.uint64)))
+    return dict(value=n_sc / t, unit=UNIT, cores=threads, kind="reference",
+                sample=f"first {R} of {n_regions} regions = {R // threads if R >= threads else 0} per thread "
+                       f"({n_sc} pairs) in {t:.2f} s; unmodified reference fill_dist_matrix, WFA2 -O3 "
+                       f"-march=x86-64-v3 (built in the CPU-only container: no AVX-512, which -march=native "
+                       f"on this host might add), static contiguous region blocks over {threads} threads"), same
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    B = workload_arrays(args.workload, 0, args.regions)
+    threads = os.cpu_count() or 1
+    base, run, _ = cpu_reference(B, 2.0, threads)
+    pairs_per_region = max(B["n_scores"] / max(B["n_regions"], 1), 1.0)
+    R = int(min(B["n_regions"], max(20 * threads, base["value"] * 8.0 / pairs_per_region)))
+    R = max(1, R - R % threads) if R >= threads else R
+    for _ in range(max(args.warmup, 0)):
+        run(min(R, max(threads, R // 4)))
+    tot_p, tot_t = 0, 0.0
+    for _ in range(args.steps):
+        n_sc, t = run(R)
+        tot_p += n_sc
+        tot_t += t
+    v = tot_p / tot_t
+    base.update(value=v, sample=f"first {R} of {B['n_regions']} regions = {R // threads if R >= threads else 0} per "
+                                f"thread, {args.steps} passes; " + base["sample"].split("; ", 1)[1])
+    base.pop("pairs"), base.pop("seconds")
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32",
+            "data": "synthetic", "config": config_dict(args.workload, B, world),
+            "cpu_baseline": base,
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def config_dict(workload, B, world):
+    c = synth.CONFIGS[workload]
+    return {"workload": f"{workload}: {c['desc']}", "regions_per_gpu": B["n_regions"],
+            "reads_per_region": c["n_reads"], "pairs_per_gpu": B["n_scores"],
+            "bases_per_gpu": int(B["bases"].size), "parallelism": f"region-sharded x{world}",
+            "l2_policy": "inputs_exceed_l2" if B["bases"].size > 126e6 else "l2_flushed_between_steps"}
+
+
+class Bench:
+    """One rank's device, context and timing helpers."""
+
+    def __init__(self, rank, world, local_rank):
+        import torch
+        import torch.distributed as dist
+        import otter_b200
+        self.torch, self.dist, self.rank, self.world, self.local_rank = torch, dist, rank, world, local_rank
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py needs a CUDA device: otter_b200 has no CPU fallback")
+        torch.cuda.set_device(local_rank)
+        self.gloo = None
+        if world > 1:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+                os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            self.gloo = dist.new_group(backend="gloo")  # host-side gathers only
+        self.ctx = otter_b200.Context(local_rank)
+        self.ext = torch.cuda.ExternalStream(self.ctx.stream, device=local_rank)
+        self.flush = None
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def reduce(self, vals):
+        """(max over ranks, sum over ranks) of a list of floats."""
+        torch = self.torch
+        t = torch.tensor(vals, dtype=torch.float64, device="cuda")
+        if self.world == 1:
+            return t.tolist(), t.tolist()
+        tmax, tsum = t.clone(), t.clone()
+        self.dist.all_reduce(tmax, op=self.dist.ReduceOp.MAX)
+        self.dist.all_reduce(tsum, op=self.dist.ReduceOp.SUM)
+        return tmax.tolist(), tsum.tolist()
+
+    def pin(self, B):
+        from otter_b200.capi import PinnedArray
+        pin = {}
+        for k in ("bases", "off", "lens", "region_start", "score_off"):
+            pa = PinnedArray(B[k].shape, B[k].dtype)
+            pa.array[...] = B[k]
+            pin[k] = pa
+        pin["out"] = PinnedArray((B["n_scores"],), np.int32)
+        return pin
+
+    @staticmethod
+    def unpin(pin):
+        for pa in pin.values():
+            pa.free()
+
+    def e2e_step(self, B, pin):
+        c = self.ctx
+        c._ck(c._l.otgpu_region_edit_scores(
+            c._h, pin["bases"].ptr, B["bases"].size, pin["off"].ptr, pin["lens"].ptr, len(B["lens"]),
+            pin["region_start"].ptr, B["n_regions"], pin["score_off"].ptr, B["n_scores"], pin["out"].ptr))
+
+    def measure(self, B, steps, warmup, sampler=None):
+        """value (device-resident, CUDA events on the library's stream) and e2e (pinned host buffers
+        -> C ABI -> host scores) of one workload on this rank; max / sum over ranks."""
+        torch = self.torch
+        ctx, ext = self.ctx, self.ext
+        pin = self.pin(B)
+        small = B["bases"].size <= 126e6
+        if small and self.flush is None:
+            self.flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+        flush = self.flush if small else None
+        for _ in range(warmup):
+            if flush is not None:  # loads torch's fill kernel outside the timed region
+                with torch.cuda.stream(ext):
+                    flush.fill_(1)
+            self.e2e_step(B, pin)
+        first = pin["out"].array.copy()
+        launches0 = ctx.stats()["kernel_launches"]
+        mark = sampler.mark() if sampler else 0
+        # ---- value: inputs resident in HBM, device time ----
+        ctx.upload_regions(pin["bases"].array, pin["off"].array, pin["lens"].array,
+                           pin["region_start"].array, pin["score_off"].array, B["n_scores"])
+        ctx.synchronize()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        stage = dict(pack=0.0, expand=0.0, align=0.0, wide=0.0)
+        self.barrier()
+        ev0.record(ext)
+        for _ in range(steps):
+            if flush is not None:
+                with torch.cuda.stream(ext):
+                    flush.fill_(1)
+            ctx.align()
+            ms = ctx.last_align_ms()  # waits for this step; per-stage CUDA events on the same stream
+            for k in stage:
+                stage[k] += ms[k]
+        ev1.record(ext)
+        self.barrier()
+        dev_ms = ev0.elapsed_time(ev1)
+        ctx.download(pin["out"].array)
+        same = bool(np.array_equal(first, pin["out"].array))
+        launches = ctx.stats()["kernel_launches"] - launches0
+        # ---- e2e: host buffers -> C ABI -> host scores, wall clock bracketed by sync ----
+        self.barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            self.e2e_step(B, pin)
+        torch.cuda.synchronize()
+        e2e_s = time.perf_counter() - t0
+        self.barrier()
+        clocks = sampler.stop(mark) if sampler else None
+        stats = ctx.stats()
+        scores = pin["out"].array.copy()
+        self.unpin(pin)
+        (dev_ms, e2e_ms), _ = self.reduce([dev_ms, e2e_s * 1e3])
+        _, (tot_pairs, tot_cells) = self.reduce([float(B["n_scores"]), float(B["cells"])])
+        k_ms = stage["align"] / steps
+        peak, peak_src = load_peaks()
+        achieved = B["alg_bytes"] / (k_ms * 1e-3) / 1e9
+        h2d = int(sum(B[k].nbytes for k in ("bases", "off", "lens", "region_start", "score_off")))
+        long_ring = B["lens"].max() > 8000
+        res = {
+            "value": tot_pairs * steps / (dev_ms * 1e-3), "ms_per_step": dev_ms / steps,
+            "gcups_equiv": tot_cells * steps / (dev_ms * 1e-3) / 1e9,
+            "e2e": {"value": tot_pairs * steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": int(B["n_scores"] * 4), "ms_per_step": e2e_ms / steps,
+                    "gcups_equiv": tot_cells * steps / (e2e_ms * 1e-3) / 1e9},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "k_align<2048>" if long_ring else "k_align<1024>",
+                         "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None,
+                         "alg_bytes_per_launch": B["alg_bytes"], "kernel_ms": k_ms,
+                         "note": "latency/issue-bound integer DP: HBM fraction is expected to be "
+                                 "tiny; see profiles/ for issue-slot and stall evidence"},
+            "stage_ms_per_step": {k: v / steps for k, v in stage.items()},
+            "pairs_8bit": stats["n_pairs_8bit"], "pairs_wide": stats["n_pairs_wide"],
+            "deterministic": same,
+        }
+        if clocks is not None:
+            res["clocks"] = clocks
+        return res, scores
+
+    # ------------------------------------------------------------------------------------------
+    def host_layer(self, B, devices, warmup, reps):
+        """The seam otter calls: fill_dist_matrices(_multi) from per-read std::strings that exist
+        before the clock starts (othost_bench_fill); staging copy, device call and score conversion
+        inside the timed region."""
+        import ctypes as C
+        H = C.CDLL(os.path.join(ROOT, "otter_b200", "lib", "libotter_b200_host.so"))
+        vp = C.c_void_p
+        H.othost_bench_fill.argtypes = [vp, vp, vp, vp, C.c_uint32, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp]
+        H.othost_bench_fill.restype = None
+        dev = np.array(devices, dtype=np.int32)
+        out = np.zeros(B["n_scores"], dtype=np.float64)
+        times = np.zeros((reps, 6), dtype=np.float64)
+        p = lambda a: a.ctypes.data_as(vp)  # noqa: E731
+        H.othost_bench_fill(p(B["bases"]), p(B["off"]), p(B["lens"]), p(B["region_start"]), B["n_regions"],
+                            p(dev), len(devices), warmup, reps, p(out), p(B["score_off"]), p(times))
+        m = times.mean(axis=0)
+        return {"value": B["n_scores"] / m[0], "unit": UNIT, "ms_per_call": 1e3 * m[0],
+                "stage_ms": {"share_total_max": 1e3 * m[1], "device_call_max": 1e3 * m[2],
+                             "wait_for_staging_copy_max": 1e3 * m[3], "score_conversion_max": 1e3 * m[4]},
+                "chunks": int(m[5]), "devices": list(map(int, devices)), "calls": reps,
+                "note": "fill_dist_matrices from std::string reads: pinned staging copy by helper threads "
+                        "and score -> dissimilarity conversion overlap the kernels chunk by chunk "
+                        "(otgpu_region_edit_scores_hooked)"}, out
+
+
+def c4_strong(bench, args):
+    """north_star's target configuration: ONE 100 k-region HiFi description (harness/synth.py C4S),
+    partitioned region-wise by estimated work over the ranks, each rank generates and aligns its
+    shard end to end from pinned host buffers, rank 0 gathers the scores on the host (gloo).  Timed
+    region = every rank's pass + the gather, max over ranks.  With more than one rank, rank 0 then
+    runs the SAME description on its one GPU so that the speed-up is measured inside one run."""
+    from harness import sharding
+    torch, dist = bench.torch, bench.dist
+    rank, world = bench.rank, bench.world
+    n_regions = args.c4_regions
+    procs = max(1, (os.cpu_count() or 1) // world)
+    t0 = time.perf_counter()
+    work = synth.c4s_work(n_regions)
+    shards = sharding.partition_regions(work, world)
+    mine = shards[rank]
+    B = synth.c4s_batch(mine, procs)
+    gen_s = time.perf_counter() - t0
+    pin = bench.pin(B)
+    reps = max(1, min(args.steps, 3))
+    n_total = 435 * n_regions
+
+    # Host-side gather (one box): a shared-memory array of all the scores in description order;
+    # every rank places its shard's rows, a gloo barrier closes the step.  No device collective.
+    shm = None
+    if world == 1:
+        full = np.empty(n_total, dtype=np.int32)
+    else:
+        from multiprocessing import shared_memory
+        name = f"otb200_c4_{os.environ.get('MASTER_PORT', '0')}"
+        if rank == 0:
+            try:
+                shared_memory.SharedMemory(name=name).unlink()  # left over from a crashed run
+            except FileNotFoundError:
+                pass
+            shm = shared_memory.SharedMemory(name=name, create=True, size=4 * n_total)
+        dist.barrier(group=bench.gloo)
+        if rank != 0:
+            shm = shared_memory.SharedMemory(name=name)
+        full = np.ndarray((n_total,), dtype=np.int32, buffer=shm.buf)
+    rows = full.reshape(n_regions, 435)
+
+    def gather(scores):
+        rows[mine] = scores.reshape(-1, 435)
+        if world > 1:
+            dist.barrier(group=bench.gloo)
+        return full
+
+    bench.e2e_step(B, pin)  # warm-up (first touch of the device buffers)
+    gather(pin["out"].array)
+    pass_ms, gather_ms, total_ms = [], [], []
+    for _ in range(reps):
+        bench.barrier()
+        t0 = time.perf_counter()
+        bench.e2e_step(B, pin)
+        t1 = time.perf_counter()
+        gather(pin["out"].array)
+        t2 = time.perf_counter()
+        (pm, tm), _ = bench.reduce([(t1 - t0) * 1e3, (t2 - t0) * 1e3])
+        pass_ms.append(pm)
+        total_ms.append(tm)
+        gather_ms.append(tm - pm)
+    chunks = bench.ctx.last_chunk_count()
+    bench.unpin(pin)
+    (load_max,), (load_sum,) = bench.reduce([float(work[mine].sum())])
+    rec = None
+    if rank == 0:
+        sec = float(np.mean(total_ms)) * 1e-3
+        rec = {"workload": f"C4S: ONE description of {n_regions} TR regions x 30 HiFi reads (per-region seeds), "
+                           f"partitioned by estimated work over {world} rank(s), generated per shard",
+               "regions": n_regions, "pairs": n_total, "n_gpus": world,
+               "seconds_per_pass": sec, "value": n_total / sec, "unit": UNIT,
+               "stage_ms": {"shard_pass_max": float(np.mean(pass_ms)), "host_gather": float(np.mean(gather_ms))},
+               "h2d_bytes_per_rank": int(B["bases"].nbytes), "gathered_bytes": int(4 * n_total),
+               "chunks_per_rank": int(chunks), "passes": reps, "generation_s": gen_s,
+               "partition_imbalance": load_max / (load_sum / world) if load_sum else 1.0,
+               "checksum": int(full.astype(np.int64).sum())}
+    if world > 1:
+        # the same description on rank 0's GPU alone (the other ranks wait)
+        if rank == 0:
+            t0 = time.perf_counter()
+            one = synth.c4s_batch(np.arange(n_regions), os.cpu_count() or 1)
+            gen1 = time.perf_counter() - t0
+            pin1 = bench.pin(one)
+            bench.e2e_step(one, pin1)
+            ts = []
+            for _ in range(max(1, min(reps, 2))):
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                bench.e2e_step(one, pin1)
+                ts.append(time.perf_counter() - t0)
+            same = bool(np.array_equal(pin1["out"].array, full))
+            bench.unpin(pin1)
+            rec["n1_seconds_per_pass"] = float(np.mean(ts))
+            rec["speedup_vs_n1"] = rec["n1_seconds_per_pass"] / rec["seconds_per_pass"]
+            rec["identical"] = same  # sharded + gathered == one GPU, score for score
+            rec["n1_generation_s"] = gen1
+            lim = "shard pass (device + H2D)" if rec["stage_ms"]["shard_pass_max"] > 4 * rec["stage_ms"]["host_gather"] else "host gather"
+            rec["limiter"] = lim
+        dist.barrier(group=bench.gloo)
+    if rank == 0:
+        rec["gather"] = "shared-memory array on the host, every rank places its shard's rows; gloo barrier" \
+            if world > 1 else "local placement"
+    if rank == 0 and not args.no_cpu_baseline:
+        # spot check against the unmodified reference: the first regions of the description
+        sub = synth.c4s_batch(np.arange(min(n_regions, 64)), 1)
+        want, _ = reference_doubles(sub, sub["n_regions"])
+        if want is not None:
+            got = scores_to_doubles(sub, full[:len(want)], len(want))
+            rec["identical_to_reference"] = bool(np.array_equal(got.view(np.uint64), want.view(np.uint64)))
+    if shm is not None:
+        del rows, full
+        dist.barrier(group=bench.gloo)
+        shm.close()
+        if rank == 0:
+            shm.unlink()
+    return rec
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -612,6 +990,10 @@ def main():
     ap.add_argument("--regions", type=int, default=None, help="override regions per GPU")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--headline-only", action="store_true",
+                    help="skip per_config / c4_strong / single_process / e2e_host_layer (kernel experiments)")
+    ap.add_argument("--c4-regions", type=int, default=synth.C4S_REGIONS,
+                    help="regions of the C4S description (c4_strong record)")
     ap.add_argument("--path", default="distmatrix", choices=["distmatrix", "consensus", "compare", "pipeline", "extract"],
                     help="distmatrix = fill_dist_matrix (the headline); consensus = the gap-affine "
                          "+ CIGAR alignments rapid_consensus issues (secondary row)")
@@ -636,156 +1018,117 @@ def main():
         run_reference(args, rank, world)
         return
 
-    import torch
-    import torch.distributed as dist
-    import otter_b200
-    from otter_b200.capi import PinnedArray
+    bench = Bench(rank, world, local_rank)
+    torch = bench.torch
+    extras = not args.headline_only and args.regions is None
 
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device: otter_b200 has no CPU fallback")
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
+    # ---- headline: the workload BASELINE.json's metric is quoted on (C2), weak scaling ----
     B = workload_arrays(args.workload, rank, args.regions)
-    n_pairs = B["n_scores"]
-    # pinned host staging: the buffers a host integration would fill while parsing reads
-    pin = {}
-    for k in ("bases", "off", "lens", "region_start", "score_off"):
-        pa = PinnedArray(B[k].shape, B[k].dtype)
-        pa.array[...] = B[k]
-        pin[k] = pa
-    out = PinnedArray((n_pairs,), np.int32)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda") \
-        if B["bases"].size <= 126e6 else None
-
-    ctx = otter_b200.Context(local_rank)
-    ext = torch.cuda.ExternalStream(ctx.stream, device=local_rank)
-
-    def e2e_step():
-        ctx._ck(ctx._l.otgpu_region_edit_scores(
-            ctx._h, pin["bases"].ptr, B["bases"].size, pin["off"].ptr, pin["lens"].ptr,
-            len(B["lens"]), pin["region_start"].ptr, B["n_regions"], pin["score_off"].ptr,
-            n_pairs, out.ptr))
-
     sampler = ClockSampler(local_rank)
     time.sleep(0.3)
+    res, scores = bench.measure(B, args.steps, args.warmup, sampler)
+    line = None
+    if rank == 0:
+        line = {"metric": METRIC, "value": res.pop("value"), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": res.pop("ms_per_step"), "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+                "config": config_dict(args.workload, B, world)}
+        line.update(res)
+        cap, why = load_capture(args.workload, B["n_regions"])
+        k_ms = line["roofline"]["kernel_ms"]
+        if cap:
+            line["roofline"]["traffic"] = cap.get("traffic_bytes_per_launch")
+            clk = (line.get("clocks") or {}).get("sm_mhz")
+            if cap.get("warp_instructions") and clk:
+                # what actually bounds the kernel: one warp instruction per sub-partition per cycle
+                n_sm = torch.cuda.get_device_properties(local_rank).multi_processor_count
+                peak_i = n_sm * 4 * clk * 1e6
+                wi = cap["warp_instructions"]
+                line["roofline"]["issue_slots"] = {
+                    "warp_instructions_per_launch": wi, "source": f"profiles/{cap['file']} (ncu, this csrc, same workload)",
+                    "achieved_per_s": wi / (k_ms * 1e-3), "peak_per_s": peak_i, "frac": wi / (k_ms * 1e-3) / peak_i}
+        else:
+            line["roofline"]["issue_slots"] = None
+            line["roofline"]["issue_slots_reason"] = why
+        if world == 1 and not args.no_cpu_baseline:
+            base, same = cpu_baseline_leg(B, scores)
+            line["cpu_baseline"] = base
+            line["identical_to_reference"] = same
+            w = work_counts(B)
+            w["offset_updates_per_s"] = w["offset_updates_per_pair"] * line["value"]
+            w["word_compares_per_s"] = w["word_compares_per_pair"] * line["value"]
+            line["work"] = w
 
-    # ---- warm-up (also first-touch of every device buffer); the timed steps follow it without
-    # an idle gap, so the SM clock is already at its load level when they start ----
-    for _ in range(args.warmup):
-        if flush is not None:  # loads torch's fill kernel outside the timed region
-            with torch.cuda.stream(ext):
-                flush.fill_(1)
-        e2e_step()
-    first = out.array.copy()
-    launches0 = ctx.stats()["kernel_launches"]
-    mark = sampler.mark()
+    # ---- the seam otter calls, same workload (N=1): fill_dist_matrices from std::string reads ----
+    if extras and world == 1:
+        hl, doubles = bench.host_layer(B, [local_rank], 1, max(2, min(args.steps, 3)))
+        hl["identical_to_c_abi"] = bool(np.array_equal(
+            doubles.view(np.uint64), scores_to_doubles(B, scores, B["n_scores"]).view(np.uint64)))
+        hl["frac_of_e2e"] = hl["value"] / line["e2e"]["value"]
+        line["e2e_host_layer"] = hl
+    del B, scores
 
-    # ---- value: inputs resident in HBM, device time ----
-    ctx.upload_regions(pin["bases"].array, pin["off"].array, pin["lens"].array,
-                       pin["region_start"].array, pin["score_off"].array, n_pairs)
-    ctx.synchronize()
-    ev0 = torch.cuda.Event(enable_timing=True)
-    ev1 = torch.cuda.Event(enable_timing=True)
-    stage = dict(pack=0.0, expand=0.0, align=0.0, wide=0.0)
-    barrier()
-    ev0.record(ext)
-    for _ in range(args.steps):
-        if flush is not None:
-            with torch.cuda.stream(ext):
-                flush.fill_(1)
-        ctx.align()
-        ms = ctx.last_align_ms()  # waits for this step; per-stage CUDA events on the same stream
-        for k in stage:
-            stage[k] += ms[k]
-    ev1.record(ext)
-    barrier()
-    dev_ms = ev0.elapsed_time(ev1)
-    ctx.download(out.array)
-    same = bool(np.array_equal(first, out.array))
-    launches = ctx.stats()["kernel_launches"] - launches0
+    # ---- the other configurations north_star names, same measurement each (N=1) ----
+    if extras and world == 1:
+        per = {}
+        for name, nreg in (("C1", None), ("C3", None)):
+            Bc = workload_arrays(name, 0, nreg)
+            r, sc = bench.measure(Bc, max(2, min(args.steps, 3)), 3)
+            r["config"] = config_dict(name, Bc, 1)
+            if not args.no_cpu_baseline:
+                r["cpu_baseline"], r["identical_to_reference"] = cpu_baseline_leg(Bc, sc, min_seconds=5.0)
+            per[name] = r
+            del Bc, sc
+        # one eighth of the 100 k-region description: the shard a rank of 8 aligns
+        from harness import sharding
+        n_desc = args.c4_regions
+        shard0 = sharding.partition_regions(synth.c4s_work(n_desc), 8)[0]
+        Bc = synth.c4s_batch(shard0, os.cpu_count() or 1)
+        x, y = synth.pair_lengths(Bc)
+        Bc["alg_bytes"] = int(((x + 3) // 4 + (y + 3) // 4 + 4).sum())
+        Bc["cells"] = int((x * y).sum())
+        r, sc = bench.measure(Bc, 2, 3)
+        r["config"] = {"workload": f"C4 shard: share 0 of 8 of the {n_desc}-region HiFi description "
+                                   f"({Bc['n_regions']} regions x 30 reads), streamed in chunks",
+                       "regions_per_gpu": Bc["n_regions"], "pairs_per_gpu": Bc["n_scores"],
+                       "bases_per_gpu": int(Bc["bases"].size), "l2_policy": "inputs_exceed_l2"}
+        if not args.no_cpu_baseline:
+            r["cpu_baseline"], r["identical_to_reference"] = cpu_baseline_leg(Bc, sc, min_seconds=5.0)
+        hl, _ = bench.host_layer(Bc, [local_rank], 1, 2)
+        hl["frac_of_e2e"] = hl["value"] / r["e2e"]["value"]
+        r["e2e_host_layer"] = hl
+        per["C4_shard"] = r
+        del Bc, sc
+        line["per_config"] = per
 
-    # ---- e2e: host buffers -> C ABI -> host scores, wall clock bracketed by sync ----
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_step()
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    barrier()
-    clocks = sampler.stop(mark)
-    stats = ctx.stats()
+    # ---- the target configuration: the 100 k-region description, strong scaling ----
+    if extras:
+        rec = c4_strong(bench, args)
+        if rank == 0:
+            line["c4_strong"] = rec
 
-    t = torch.tensor([dev_ms, e2e_s * 1e3, float(n_pairs), float(B["cells"])], dtype=torch.float64,
-                     device="cuda")
-    if world > 1:
-        tmax = t.clone()
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        tsum = t.clone()
-        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        dev_ms, e2e_ms = tmax[0].item(), tmax[1].item()
-        tot_pairs, tot_cells = tsum[2].item(), tsum[3].item()
-    else:
-        e2e_ms = e2e_s * 1e3
-        tot_pairs, tot_cells = float(n_pairs), float(B["cells"])
+    # ---- one host process feeding all N devices (rank 0 only; the other ranks wait) ----
+    if extras and world > 1:
+        if rank == 0:
+            n_desc = args.c4_regions
+            ids = np.arange(min(n_desc, 1500 * world))
+            Bm = synth.c4s_batch(ids, os.cpu_count() or 1)
+            multi, dm = bench.host_layer(Bm, list(range(world)), 1, 2)
+            single, d1 = bench.host_layer(Bm, [0], 1, 1)
+            multi["multi_identical"] = bool(np.array_equal(dm.view(np.uint64), d1.view(np.uint64)))
+            multi["single_device_ms_per_call"] = single["ms_per_call"]
+            multi["speedup_vs_one_device"] = single["ms_per_call"] / multi["ms_per_call"]
+            multi["workload"] = f"first {len(ids)} regions of the C4S description ({Bm['n_scores']} pairs, " \
+                                f"{Bm['bases'].size >> 20} MB of reads) from ONE host process"
+            multi["gather"] = "none: every region's DistMatrix is filled in place by the thread that owns its device"
+            line["single_process"] = multi
+        bench.dist.barrier(group=bench.gloo)
 
     if rank == 0:
-        peak, peak_src = load_peaks()
-        k_ms = stage["align"] / args.steps
-        achieved = B["alg_bytes"] / (k_ms * 1e-3) / 1e9
-        value = tot_pairs * args.steps / (dev_ms * 1e-3)
-        e2e_v = tot_pairs * args.steps / (e2e_ms * 1e-3)
-        h2d = int(sum(B[k].nbytes for k in ("bases", "off", "lens", "region_start", "score_off")))
-        line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
-            "config": config_dict(args, B, world),
-            "gcups_equiv": tot_cells * args.steps / (dev_ms * 1e-3) / 1e9,
-            "e2e": {"value": e2e_v, "unit": UNIT, "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": int(n_pairs * 4), "ms_per_step": e2e_ms / args.steps,
-                    "gcups_equiv": tot_cells * args.steps / (e2e_ms * 1e-3) / 1e9},
-            "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k_align<2048>" if B["lens"].max() > 8000 else "k_align<1024>", "achieved": achieved,
-                         "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": load_traffic(args.workload, B["n_regions"]),
-                         "alg_bytes_per_launch": B["alg_bytes"], "kernel_ms": k_ms,
-                         "note": "latency/issue-bound integer DP: HBM fraction is expected to be "
-                                 "tiny; see profiles/ for issue-slot and stall evidence"},
-            "stage_ms_per_step": {k: v / args.steps for k, v in stage.items()},
-            "pairs_8bit": stats["n_pairs_8bit"], "pairs_wide": stats["n_pairs_wide"],
-            "deterministic": same, "clocks": clocks,
-        }
-        wi = load_warp_instructions(args.workload, B["n_regions"])
-        if wi and clocks.get("sm_mhz"):
-            # what actually bounds the kernel: one warp instruction per sub-partition per cycle
-            n_sm = torch.cuda.get_device_properties(local_rank).multi_processor_count
-            peak_i = n_sm * 4 * clocks["sm_mhz"] * 1e6
-            line["roofline"]["issue_slots"] = {
-                "warp_instructions_per_launch": wi, "source": "profiles/r1f_traffic.json (ncu, same workload)",
-                "achieved_per_s": wi / (k_ms * 1e-3), "peak_per_s": peak_i,
-                "frac": wi / (k_ms * 1e-3) / peak_i}
-        if world == 1 and not args.no_cpu_baseline:
-            base, _, _ = cpu_reference(B, 15.0)
-            base.pop("pairs"), base.pop("seconds")
-            line["cpu_baseline"] = base
-            w = work_counts(B)
-            w["offset_updates_per_s"] = w["offset_updates_per_pair"] * value
-            w["word_compares_per_s"] = w["word_compares_per_pair"] * value
-            line["work"] = w
         print(json.dumps(line), flush=True)
-    ctx.close()
+    bench.ctx.close()
     if world > 1:
-        dist.destroy_process_group()
+        bench.dist.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -123,3 +123,64 @@ def pair_lengths(B):
     if not xs:
         return np.zeros(0, np.int64), np.zeros(0, np.int64)
     return np.concatenate(xs), np.concatenate(ys)
+
+
+# ---- the 100 k-region HiFi description of BASELINE.json configs[3] / north_star ("C4S") -----------
+# Every region has its own seed, so any rank can generate any region: one description, generated
+# per shard on the fly, partitioned by estimated work, nothing shipped between ranks.
+C4S_SEED = 0xB2004
+C4S_REGIONS = 100_000
+
+
+def c4s_target_len(g):
+    return int(np.random.default_rng([C4S_SEED, int(g)]).integers(2000, 5001))
+
+
+def c4s_region(g):
+    rng = np.random.default_rng([C4S_SEED, int(g)])
+    tl = int(rng.integers(2000, 5001))  # the first draw: c4s_target_len reproduces it
+    return tr_region(rng, 30, tl, 0.005, flank=100)
+
+
+def c4s_work(n_regions=C4S_REGIONS):
+    """Estimated alignment work per region from its header alone (30 reads of about tl bases:
+    pairs x |x| x |y| grows with tl^2), without generating a read."""
+    tl = np.array([c4s_target_len(g) for g in range(n_regions)], dtype=np.float64)
+    return tl * tl
+
+
+def _c4s_pack(gs):
+    lens, parts = [], []
+    for g in gs:
+        reg = c4s_region(g)
+        lens += [len(r) for r in reg]
+        parts += reg
+    return (np.concatenate(parts).astype(np.uint8) if parts else np.zeros(0, np.uint8),
+            np.array(lens, dtype=np.uint32), len(gs))
+
+
+def c4s_batch(region_ids, procs=1):
+    """Flat arrays (region ABI) of the listed regions of the description, in the listed order;
+    generated by `procs` worker processes."""
+    region_ids = [int(g) for g in region_ids]
+    if procs > 1 and len(region_ids) >= 4 * procs:
+        import multiprocessing as mp
+        per = max(50, (len(region_ids) + 8 * procs - 1) // (8 * procs))
+        chunks = [region_ids[i:i + per] for i in range(0, len(region_ids), per)]
+        with mp.get_context("fork").Pool(procs) as pool:
+            outs = pool.map(_c4s_pack, chunks)
+    else:
+        outs = [_c4s_pack(region_ids)]
+    bases = np.concatenate([o[0] for o in outs]) if outs else np.zeros(0, np.uint8)
+    lens = np.concatenate([o[1] for o in outs]) if outs else np.zeros(0, np.uint32)
+    n_reg = len(region_ids)
+    off = np.zeros(len(lens), dtype=np.uint64)
+    if len(lens):
+        off[1:] = np.cumsum(lens[:-1], dtype=np.uint64)
+    rs = np.arange(n_reg + 1, dtype=np.uint32) * 30
+    npairs = np.full(n_reg, 435, dtype=np.uint64)
+    so = np.zeros(n_reg, dtype=np.uint64)
+    if n_reg:
+        so[1:] = np.cumsum(npairs[:-1])
+    return dict(bases=bases, off=off, lens=lens, region_start=rs, score_off=so,
+                n_scores=int(npairs.sum()), n_regions=n_reg)

@@ -16,6 +16,7 @@ SYMBOLS = [
     "otgpu_batch_download", "otgpu_synchronize", "otgpu_last_align_ms", "otgpu_affine_cigars",
     "otgpu_edit_cigars", "otgpu_last_chunk_count", "otgpu_affine_cigars_packed",
     "otgpu_edit_cigars_packed", "otgpu_extract_reads", "otgpu_kde_densities",
+    "otgpu_region_edit_scores_hooked",
 ]
 
 
@@ -85,6 +86,7 @@ def lib():
         l.otgpu_host_free.restype = None
         l.otgpu_edit_scores.argtypes = [vp, vp, u64, vp, vp, u32, vp, u64, vp]
         l.otgpu_region_edit_scores.argtypes = [vp, vp, u64, vp, vp, u32, vp, u32, vp, u64, vp]
+        l.otgpu_region_edit_scores_hooked.argtypes = [vp, vp, u64, vp, vp, u32, vp, u32, vp, u64, vp, vp]
         l.otgpu_batch_upload_regions.argtypes = [vp, vp, u64, vp, vp, u32, vp, u32, vp, u64]
         l.otgpu_batch_upload_pairs.argtypes = [vp, vp, u64, vp, vp, u32, vp, u64]
         l.otgpu_batch_align.argtypes = [vp]
@@ -178,6 +180,24 @@ class Context:
         self._ck(self._l.otgpu_region_edit_scores(self._h, _p(bases), bases.size, _p(off), _p(lens),
                                                   len(lens), _p(region_start), len(region_start) - 1,
                                                   _p(score_off), n_scores, _p(out)))
+        return out
+
+    def region_edit_scores_hooked(self, bases, off, lens, region_start, score_off, n_scores,
+                                  wait_bases=None, scores_ready=None):
+        """otgpu_region_edit_scores_hooked: wait_bases(upto_byte) is called before the library first
+        reads bases[:upto_byte], scores_ready(first, n) once out[first:first+n] is final."""
+        WAIT = C.CFUNCTYPE(None, C.c_void_p, C.c_uint64)
+        READY = C.CFUNCTYPE(None, C.c_void_p, C.c_uint64, C.c_uint64)
+
+        class Hooks(C.Structure):
+            _fields_ = [("wait_bases", WAIT), ("scores_ready", READY), ("user", C.c_void_p)]
+        out = np.empty(n_scores, dtype=np.int32)
+        h = Hooks(WAIT(lambda u, upto: wait_bases(int(upto)) if wait_bases else None),
+                  READY(lambda u, a, n: scores_ready(int(a), int(n), out) if scores_ready else None), None)
+        self._ck(self._l.otgpu_region_edit_scores_hooked(
+            self._h, _p(bases), C.c_uint64(bases.size), _p(off), _p(lens), C.c_uint32(len(lens)),
+            _p(region_start), C.c_uint32(len(region_start) - 1), _p(score_off), C.c_uint64(n_scores),
+            _p(out), C.byref(h)))
         return out
 
     def last_chunk_count(self):

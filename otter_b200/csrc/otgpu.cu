@@ -764,7 +764,10 @@ static int region_scores_streamed(otgpu_ctx* ctx, const uint8_t* bases, const ui
     // (trailing regions without reads: region_start[g0] == n_reads, nothing left to address)
     const uint64_t base0 = region_start[g0] < region_start[n_regions] ? read_off[region_start[g0]] : 0;
     uint64_t bytes = 0;
-    while (g1 < n_regions && (g1 == g0 || bytes < chunk_bases || region_start[g1] == region_start[n_regions])) {
+    // with hooks the first chunks are small (1/8, 1/4, 1/2 of the chunk size): the caller's staging
+    // copy of the first chunk is the one wait nothing can hide
+    const uint64_t want = hooks ? chunk_bases >> (chunks < 3 ? 3 - chunks : 0) : chunk_bases;
+    while (g1 < n_regions && (g1 == g0 || bytes < want || region_start[g1] == region_start[n_regions])) {
       const uint32_t ra = region_start[g1], rb = region_start[g1 + 1];
       if (rb > ra) bytes = read_off[rb - 1] + read_len[rb - 1] - base0;
       ++g1;
@@ -839,7 +842,7 @@ int otgpu_region_edit_scores_hooked(otgpu_ctx* ctx, const uint8_t* bases, uint64
   // with hooks the chunks are smaller: their purpose is overlap with the caller's own work
   const uint64_t chunk = hooked ? (ctx ? ctx->hook_chunk_bases : 0) : (ctx ? ctx->chunk_bases : 0);
   if (ctx && bases && read_off && read_len && region_start && score_off && scores_out &&
-      n_regions > 1 && n_bases > chunk + chunk / 2) {
+      n_regions > 1 && n_bases > (hooked ? chunk / 4 : chunk + chunk / 2)) {
     // streaming needs reads and scores laid out region after region, which is how every caller
     // here builds them; verify (the tables only - the bases may still be on their way), else fall
     // through to the single batch

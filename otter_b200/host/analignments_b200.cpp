@@ -243,7 +243,7 @@ void fill_dist_matrices(const bool& ignore_haps, wfa::WFAligner& aligner,
   // The copy into pinned staging is the longest host step of a wave.  Worker threads run it front
   // to back and publish a watermark; in the all-spanning case (below) the device call starts at
   // once and waits, chunk by chunk, only for the bytes it is about to upload.
-  const int workers = total > ((size_t)8 << 20) ? 4 : 1;
+  const int workers = total > ((size_t)8 << 20) ? 6 : 1;
   const size_t n_seqs = seqs.size();
   constexpr size_t kBlock = 64;  // reads per unit of work
   const size_t n_blocks = (n_seqs + kBlock - 1) / kBlock;

@@ -392,3 +392,118 @@ def test_streamed_chunks_equal_single_batch(ctx):
                 assert c2.stats()["n_pairs"] == B["n_scores"]
     finally:
         del os.environ["OTGPU_CHUNK_MB"]
+
+
+def test_streamed_batch_with_trailing_empty_regions(built):
+    """A streamed batch whose last regions hold no reads (region_start[g] == n_reads): they are
+    folded into the last chunk instead of starting a chunk that would address read n_reads."""
+    import otter_b200
+    rng = np.random.default_rng(405)
+    regions = [S.tr_region(rng, 10, int(rng.integers(1500, 3000)), 0.03, extra_frac=0.2) for _ in range(70)]
+    regions += [[], [], []]
+    B = S.region_batch(regions)
+    with otter_b200.Context(0) as c1:
+        exp = c1.region_edit_scores(B["bases"], B["off"], B["lens"], B["region_start"], B["score_off"],
+                                    B["n_scores"])
+    os.environ["OTGPU_CHUNK_MB"] = "1"
+    try:
+        with otter_b200.Context(0) as c2:
+            got = c2.region_edit_scores(B["bases"], B["off"], B["lens"], B["region_start"],
+                                        B["score_off"], B["n_scores"])
+            assert c2.last_chunk_count() >= 2
+    finally:
+        del os.environ["OTGPU_CHUNK_MB"]
+    assert np.array_equal(got, exp)
+
+
+def test_hooked_call_waits_for_bases_and_hands_scores_back_in_order(built):
+    """otgpu_region_edit_scores_hooked: the caller fills `bases` while the call runs.  Here the
+    buffer starts as garbage and wait_bases copies the real bytes in only as far as it is asked to;
+    scores_ready must cover the score array once, in order, and every range must already hold
+    its final values when the hook runs."""
+    import otter_b200
+    rng = np.random.default_rng(406)
+    regions = [S.tr_region(rng, 9, int(rng.integers(1500, 3500)), 0.04, extra_frac=0.3) for _ in range(200)]
+    B = S.region_batch(regions)
+    with otter_b200.Context(0) as c1:
+        exp = c1.region_edit_scores(B["bases"], B["off"], B["lens"], B["region_start"], B["score_off"],
+                                    B["n_scores"])
+    os.environ["OTGPU_CHUNK_MB"] = "1"
+    try:
+        with otter_b200.Context(0) as c2:
+            late = np.full_like(B["bases"], ord("T"))
+            filled, asked, ready = [0], [], []
+
+            def wait_bases(upto):
+                asked.append(upto)
+                late[filled[0]:upto] = B["bases"][filled[0]:upto]
+                filled[0] = max(filled[0], upto)
+
+            def scores_ready(first, n, out):
+                ready.append((first, n))
+                assert np.array_equal(out[first:first + n], exp[first:first + n])
+
+            got = c2.region_edit_scores_hooked(late, B["off"], B["lens"], B["region_start"], B["score_off"],
+                                               B["n_scores"], wait_bases, scores_ready)
+            chunks = c2.last_chunk_count()
+    finally:
+        del os.environ["OTGPU_CHUNK_MB"]
+    assert np.array_equal(got, exp)
+    assert chunks >= 3 and len(asked) == chunks and len(ready) == chunks
+    assert asked == sorted(asked) and asked[-1] == B["bases"].size and asked[0] < B["bases"].size
+    at = 0
+    for first, n in ready:
+        assert first == at
+        at += n
+    assert at == B["n_scores"]
+
+
+def test_host_layer_overlapped_staging_equals_single_batch(built):
+    """fill_dist_matrices feeds the hooked call from worker threads (staging copy of chunk i+1 and
+    score conversion of chunk i-1 under the kernels of chunk i): same matrices as one batch, also
+    with regions that have no pairs at either end."""
+    H = host_lib()
+    rng = np.random.default_rng(407)
+    regions = [[]] + [S.tr_region(rng, int(n), int(l), 0.03, extra_frac=0.3)
+                      for n, l in zip(rng.integers(1, 12, 900), rng.integers(800, 2500, 900))] + [[], []]
+    B = S.region_batch(regions)
+    assert B["bases"].size > (9 << 20)   # large enough for the helper threads
+    one = np.zeros(B["n_scores"])
+    H.othost_fill_dist_matrices(S.ptr(B["bases"]), S.ptr(B["off"]), S.ptr(B["lens"]), None,
+                                S.ptr(B["region_start"]), len(regions), S.ptr(one), S.ptr(B["score_off"]))
+    os.environ["OTGPU_CHUNK_MB"] = "1"
+    try:
+        import subprocess, sys, textwrap
+        # a fresh process: the host layer's aligner (and its context's chunk size) is made once per thread
+        code = textwrap.dedent("""
+            import sys, numpy as np
+            sys.path.insert(0, %r); sys.path.insert(0, %r)
+            import support as S, test_gpu_parity as T
+            Z = np.load(sys.argv[1])
+            B = {k: Z[k] for k in Z.files}   # (NpzFile makes a fresh array per access)
+            H = T.host_lib()
+            out = np.zeros(int(B["n_scores"]))
+            H.othost_fill_dist_matrices(S.ptr(B["bases"]), S.ptr(B["off"]), S.ptr(B["lens"]), None,
+                                        S.ptr(B["region_start"]), len(B["region_start"]) - 1, S.ptr(out),
+                                        S.ptr(B["score_off"]))
+            np.save(sys.argv[2], out)
+        """ % (ROOT, os.path.join(ROOT, "tests")))
+        import tempfile
+        d = tempfile.mkdtemp()
+        np.savez(os.path.join(d, "b.npz"), bases=B["bases"], off=B["off"], lens=B["lens"],
+                 region_start=B["region_start"], score_off=B["score_off"], n_scores=B["n_scores"])
+        subprocess.check_call([sys.executable, "-c", code, os.path.join(d, "b.npz"), os.path.join(d, "o.npy")])
+        got = np.load(os.path.join(d, "o.npy"))
+    finally:
+        del os.environ["OTGPU_CHUNK_MB"]
+    assert np.array_equal(got, one)
+    P = S.port()
+    g = 5
+    reg = regions[g]
+    bases, off, lens = S.pack_reads(reg)
+    n = len(reg) * (len(reg) - 1) // 2
+    if n:
+        exp = np.zeros(n)
+        P.wfo_fill_dist_matrix(S.ptr(bases), S.ptr(off), S.ptr(lens), None,
+                               S.ptr(np.arange(len(reg), dtype=np.int32)), len(reg), S.ptr(exp))
+        assert np.array_equal(one[int(B["score_off"][g]):int(B["score_off"][g]) + n], exp)
