@@ -465,9 +465,9 @@ def test_host_layer_overlapped_staging_equals_single_batch(built):
     H = host_lib()
     rng = np.random.default_rng(407)
     regions = [[]] + [S.tr_region(rng, int(n), int(l), 0.03, extra_frac=0.3)
-                      for n, l in zip(rng.integers(1, 12, 900), rng.integers(800, 2500, 900))] + [[], []]
+                      for n, l in zip(rng.integers(1, 12, 1300), rng.integers(800, 2500, 1300))] + [[], []]
     B = S.region_batch(regions)
-    assert B["bases"].size > (9 << 20)   # large enough for the helper threads
+    assert B["bases"].size > (10 << 20)   # large enough for the helper threads (> 8 MiB)
     one = np.zeros(B["n_scores"])
     H.othost_fill_dist_matrices(S.ptr(B["bases"]), S.ptr(B["off"]), S.ptr(B["lens"]), None,
                                 S.ptr(B["region_start"]), len(regions), S.ptr(one), S.ptr(B["score_off"]))
