@@ -594,10 +594,10 @@ def load_capture(workload, n_regions):
     return j, None
 
 
-def reference_doubles(B, R, threads=None):
+def reference_doubles(B, R, threads=None, so="libotter_ref.so"):
     """The unmodified reference's dissimilarities of the first R regions (oracle/_ref), or None."""
     import ctypes as C
-    ref_so = os.path.join(ROOT, "oracle", "_ref", "libotter_ref.so")
+    ref_so = os.path.join(ROOT, "oracle", "_ref", so)
     if not os.path.exists(ref_so) or R < 1:
         return None, 0.0
     lib = C.CDLL(ref_so)
@@ -630,7 +630,34 @@ def scores_to_doubles(B, scores, n_sc):
     return out
 
 
-def cpu_baseline_leg(B, scores, regions_per_thread=20, min_seconds=8.0):
+def cpu_variants(B, R, threads, want):
+    """The same reference sources under the other two builds BASELINE.md lists, on the first R
+    regions: WFA2-lib as otter's README builds it (-Wall -g, no -O), and -O3 -march=x86-64-v4 where
+    the host has AVX-512 (what -march=native could add over the -march=x86-64-v3 library that
+    travels).  Results must equal the main build's."""
+    out = {}
+    try:
+        flags = open("/proc/cpuinfo").read()
+    except OSError:
+        flags = ""
+    avx512 = all(f in flags for f in ("avx512f", "avx512bw", "avx512vl", "avx512dq"))
+    for key, so, ok in (("readme_build_-g", "libotter_ref_readme.so", True),
+                        ("O3_march_x86-64-v4", "libotter_ref_v4.so", avx512)):
+        if not ok:
+            out[key] = "host has no AVX-512"
+            continue
+        got, t = reference_doubles(B, R, threads, so)
+        if got is None:
+            out[key] = "library not built"
+            continue
+        out[key] = {"value": len(got) / t, "unit": UNIT, "regions": R, "seconds": t,
+                    "same_results": bool(np.array_equal(got.view(np.uint64), want[:len(got)].view(np.uint64)))}
+    g3, t = reference_doubles(B, R, threads)
+    out["O3_march_x86-64-v3_same_sample"] = {"value": len(g3) / t, "unit": UNIT, "regions": R, "seconds": t}
+    return out
+
+
+def cpu_baseline_leg(B, scores, regions_per_thread=20, min_seconds=8.0, with_variants=False):
     """The reference's fill_dist_matrix on all host threads over the first R regions, R >= 20 per
     thread (static contiguous blocks: fewer and the slowest block sets the number), and the check
     of the GPU scores of those regions against its doubles."""
@@ -653,7 +680,10 @@ def cpu_baseline_leg(B, scores, regions_per_thread=20, min_seconds=8.0):
     if scores is not None:
         mine = scores_to_doubles(B, scores, n_sc)
         same = bool(np.array_equal(mine.view(np.uint64), want.view(np.uint64)))
-    return dict(value=n_sc / t, unit=UNIT, cores=threads, kind="reference",
+    variants = None
+    if with_variants:
+        variants = cpu_variants(B, max(threads, min(R, 8 * threads)), threads, want)
+    return dict(value=n_sc / t, unit=UNIT, cores=threads, kind="reference", other_builds=variants,
                 sample=f"first {R} of {n_regions} regions = {R // threads if R >= threads else 0} per thread "
                        f"({n_sc} pairs) in {t:.2f} s; unmodified reference fill_dist_matrix, WFA2 -O3 "
                        f"-march=x86-64-v3 (built in the CPU-only container: no AVX-512, which -march=native "
@@ -1051,7 +1081,7 @@ def main():
             line["roofline"]["issue_slots"] = None
             line["roofline"]["issue_slots_reason"] = why
         if world == 1 and not args.no_cpu_baseline:
-            base, same = cpu_baseline_leg(B, scores)
+            base, same = cpu_baseline_leg(B, scores, with_variants=extras)
             line["cpu_baseline"] = base
             line["identical_to_reference"] = same
             w = work_counts(B)

@@ -884,10 +884,11 @@ k_affine(DevBatch b, Counters* __restrict__ ctr, const uint32_t* __restrict__ or
          uint32_t* __restrict__ ovf_list, AffPen pen,
          int32_t* __restrict__ rings, int wcap, int n_rings, uint8_t* __restrict__ slab, uint32_t slab_bytes,
          uint8_t* __restrict__ ops, uint32_t ops_cap, const uint64_t* __restrict__ cigar_off,
-         char* __restrict__ cigars, int32_t* __restrict__ cigar_len) {
+         char* __restrict__ cigars, int32_t* __restrict__ cigar_len, int max_warps) {
   __shared__ AffSlot meta_smem[kWarpsPerCta][EDIT ? 1 : kAffMaxScope];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const size_t gw = (size_t)blockIdx.x * kWarpsPerCta + warp;
+  if (max_warps > 0 && gw >= (size_t)max_warps) return;  // retry tier: only the warps that own a slab
   AffWork W;
   W.rstride = wcap + kRingPad;
   W.rings = rings + gw * (size_t)n_rings * W.rstride;
@@ -1079,22 +1080,26 @@ int cigars_impl(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const ui
   (edit ? k_affine<false, true> : k_affine<false, false>)<<<grid, kCtaThreads, 0, st>>>(
       b, ctr, order, ovf, pen, static_cast<int32_t*>(ctx->aff_rings.p), wcap, n_rings,
       static_cast<uint8_t*>(ctx->aff_slab.p), slab1, static_cast<uint8_t*>(ctx->aff_ops.p), ops_cap,
-      d_cigar_off, static_cast<char*>(ctx->cigars.p), static_cast<int32_t*>(ctx->cigar_len.p));
+      d_cigar_off, static_cast<char*>(ctx->cigars.p), static_cast<int32_t*>(ctx->cigar_len.p), 0);
   ctx->stats.kernel_launches += 2;
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(ctx->h_counters, ctx->counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   const unsigned long long n_retry = static_cast<const Counters*>(ctx->h_counters)->v[1];
-  if (n_retry) {  // traces that outgrew 2 MiB: few warps, big slabs
+  bool free_slab2 = false;
+  if (n_retry) {  // traces that outgrew 2 MiB: few warps, big slabs - one slab per retried pair, at
+    // most 32 of them (8 GiB), never more warps than the rings and op buffers were sized for
     const uint32_t slab2 = 256u << 20;
-    int grid2 = (int)((n_retry + kWarpsPerCta - 1) / kWarpsPerCta);
-    if (grid2 > 8) grid2 = 8;
-    RS(aff_slab2, (size_t)grid2 * kWarpsPerCta * slab2);
+    int warps2 = (int)(n_retry < 32 ? n_retry : 32);
+    if (warps2 > grid * kWarpsPerCta) warps2 = grid * kWarpsPerCta;
+    const int grid2 = (warps2 + kWarpsPerCta - 1) / kWarpsPerCta;
+    RS(aff_slab2, (size_t)warps2 * slab2);
+    free_slab2 = true;
     (edit ? k_affine<true, true> : k_affine<true, false>)<<<grid2, kCtaThreads, 0, st>>>(
         b, ctr, order, ovf, pen, static_cast<int32_t*>(ctx->aff_rings.p), wcap, n_rings,
         static_cast<uint8_t*>(ctx->aff_slab2.p), slab2, static_cast<uint8_t*>(ctx->aff_ops.p),
         ops_cap, d_cigar_off, static_cast<char*>(ctx->cigars.p),
-        static_cast<int32_t*>(ctx->cigar_len.p));
+        static_cast<int32_t*>(ctx->cigar_len.p), warps2);
     ctx->stats.kernel_launches++;
     CK(cudaGetLastError());
   }
@@ -1137,6 +1142,11 @@ int cigars_impl(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const ui
     CK(cudaMemcpyAsync(cigars_out, ctx->cigars.p, cig_bytes, cudaMemcpyDeviceToHost, st));
   }
   CK(cudaStreamSynchronize(st));
+  if (free_slab2 && ctx->aff_slab2.p) {  // gigabytes, needed by a handful of alignments: give them back
+    cudaFree(ctx->aff_slab2.p);
+    ctx->aff_slab2.p = nullptr;
+    ctx->aff_slab2.cap = 0;
+  }
   ctx->stats.n_pairs = n_pairs;
   ctx->stats.n_pairs_wide = n_retry;
   return OTGPU_OK;

@@ -5,6 +5,9 @@
 #include <cstring>
 #include <iostream>
 
+#include <mutex>
+
+#include "device_turn.hpp"
 #include "otter_b200.h"
 
 template <class T>
@@ -65,10 +68,12 @@ void ReadExtractor::extract(wfa::WFAligner& aligner, bool omitnonspanning,
   std::vector<uint32_t> len(n);
   const char* bases = nullptr;
   const uint64_t* begin = nullptr;
-  const int st = ctx ? otgpu_extract_reads(ctx, in.data(), n, cigar_.data(), cigar_.size(), seq4_.data(),
-                                           seq4_.size(), status.data(), coords.data(), len.data(),
-                                           &bases, &begin)
-                     : OTGPU_ERR_NO_DEVICE;
+  int st = OTGPU_ERR_NO_DEVICE;
+  if (ctx) {
+    std::lock_guard<otb200::DeviceTurn> turn(otb200::device_turn(aligner.device()));
+    st = otgpu_extract_reads(ctx, in.data(), n, cigar_.data(), cigar_.size(), seq4_.data(), seq4_.size(),
+                             status.data(), coords.data(), len.data(), &bases, &begin);
+  }
   if (st != OTGPU_OK) {
     std::cerr << "ERROR: otter_b200 read extraction: " << otgpu_strerror(st) << " ("
               << (ctx ? otgpu_last_cuda_error(ctx) : "") << ")" << std::endl;

@@ -163,6 +163,34 @@ void othost_bench_fill(const char* bases, const uint64_t* off, const uint32_t* l
       std::memcpy(out + out_off[g], dms[g].values.data(), dms[g].values.size() * sizeof(double));
 }
 
+// rapid_consensus_alignments for one region (reads with labels[i] >= 0 are clustered; valid =
+// spanning reads, their distance matrix filled first): the member CIGARs of every label, in plan
+// order, each terminated by '\n', written to `out` (truncated to cap).  Returns the bytes needed.
+uint64_t othost_consensus_cigars(const char* bases, const uint64_t* off, const uint32_t* len,
+                                 const uint8_t* span, uint32_t n_reads, const int* labels_in,
+                                 int total_alleles, char* out, uint64_t cap) {
+  auto reads = build_reads(bases, off, len, span, 0, n_reads);
+  std::vector<int> labels(labels_in, labels_in + n_reads), valid;
+  for (int i = 0; i < (int)n_reads; ++i)
+    if (reads[i].is_spanning()) valid.push_back(i);
+  DistMatrix dm((uint32_t)valid.size());
+  fill_dist_matrix(true, aligner(), reads, valid, dm);
+  static thread_local std::unique_ptr<wfa::WFAlignerGapAffine> a2;
+  if (!a2) a2.reset(new wfa::WFAlignerGapAffine(4, 6, 2, wfa::WFAligner::Alignment, wfa::WFAligner::MemoryMed));
+  std::vector<ConsensusJob> jobs(1);
+  jobs[0].reads = &reads;
+  jobs[0].labels = &labels;
+  jobs[0].valid_indeces = &valid;
+  jobs[0].total_alleles = total_alleles;
+  jobs[0].valid_distmatrix = &dm;
+  rapid_consensus_alignments(*a2, jobs);
+  std::string all;
+  for (const ConsensusPlan& P : jobs[0].plans)
+    for (const std::string& c : P.cigars) { all += c; all += '\n'; }
+  if (out && cap) std::memcpy(out, all.data(), std::min<uint64_t>(cap, all.size()));
+  return all.size();
+}
+
 // The partition alone (no device needed): part_out[g] = share of region g, loads_out[p] = the
 // estimated work of share p.
 void othost_partition_regions(const uint32_t* len, const uint32_t* region_start, uint32_t n_regions,

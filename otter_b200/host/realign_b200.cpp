@@ -250,9 +250,14 @@ void rapid_consensus_alignments(wfa::WFAligner& aligner2, std::vector<ConsensusJ
   }
   std::vector<std::string> cigars;
   affine_cigars(aligner2, cj, cigars);
-  // getAlignmentCigar() after a skipped call returns the previous alignment's CIGAR (:280): replay
-  // that with a running "last CIGAR", in the order a single reference thread would have run
-  // (each CIGAR is moved to its plan, not copied: they are the bulk of the host-side bytes)
+  // getAlignmentCigar() after a skipped call returns the previous alignment's CIGAR (:280): within a
+  // batch that is replayed with a running "last CIGAR", in the order a single reference thread
+  // would have run (each CIGAR is moved to its plan, not copied: they are the bulk of the
+  // host-side bytes).  DELIBERATE DIVERGENCE for a skipped call that comes FIRST in a batch: the
+  // reference then inserts whatever its thread-local aligner produced last - in an earlier region
+  // of that thread's block, or in local_realignment - i.e. a value that depends on the thread
+  // schedule; here it is the facade's own last single-call CIGAR (empty unless the caller made
+  // one), which is deterministic.  tests/test_gpu_affine.py pins this.
   const std::string initial = aligner2.getAlignmentCigar();
   const std::string* last = &initial;
   size_t q = 0;

@@ -2,9 +2,11 @@
 // (shim/bindings/cpp/WFAligner.hpp) on top of the C ABI.  One pair per call.
 #include <cstdint>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "bindings/cpp/WFAligner.hpp"
+#include "device_turn.hpp"
 #include "otter_b200.h"
 
 namespace wfa {
@@ -34,6 +36,8 @@ WFAligner::AlignmentStatus WFAligner::run(const char* p, int plen, const char* t
   const uint32_t len[2] = {(uint32_t)plen, (uint32_t)tlen};
   otgpu_pair pr{0, 1, endsfree ? pb : -1, pe, tb, te};
   int32_t sc = 0;
+  // one whole-GPU call at a time per device, also for single alignments (device_turn.hpp)
+  std::lock_guard<otb200::DeviceTurn> turn(otb200::device_turn(device_));
   if (kind_ == kGapAffine || scope_ == Alignment) {
     // score + CIGAR in one launch: gap-affine (wfa_affine.cuh) or, for the aligner `compare`
     // builds (reference src/compare.cpp:95), edit distance with CIGAR (wfa_edit_cigar.cuh)

@@ -262,3 +262,42 @@ def test_wave_of_regions_equals_reference(built):
         finally:
             del os.environ["OTREF_WAVE"], os.environ["OTREF_ISSUERS"]
         assert nc == na and lc == la and dc == da, issuers
+
+
+def test_skipped_consensus_call_replays_the_last_cigar_deterministically(built):
+    """src/analignments.cpp:262-281: a member longer than the representative and spanning on
+    neither side gets NO aligner call, and the reference inserts whatever CIGAR its thread-local
+    aligner holds.  Inside a batch that is the previous member's CIGAR (reproduced); for a skipped
+    call that comes first it is schedule-dependent in the reference, and deliberately the facade's
+    own last single-call CIGAR here (empty in a fresh thread) - realign_b200.cpp."""
+    import ctypes as C
+    H = C.CDLL(os.path.join(ROOT, "otter_b200", "lib", "libotter_b200_host.so"))
+    vp = C.c_void_p
+    H.othost_consensus_cigars.restype = C.c_uint64
+    H.othost_consensus_cigars.argtypes = [vp, vp, vp, vp, C.c_uint32, vp, C.c_int, C.c_char_p, C.c_uint64]
+    rng = np.random.default_rng(12)
+    base = S.rand_seq(rng, 300)
+    longer = np.concatenate([base, S.rand_seq(rng, 40)])      # longer than any representative
+    spanning = [S.mutate(rng, base, 0.01) for _ in range(4)]
+
+    def run(order):
+        reads, span = [], []
+        for kind in order:
+            if kind == "L":
+                reads.append(longer); span.append(0)          # spanning on neither side
+            else:
+                reads.append(spanning[int(kind)]); span.append(3)
+        bases, off, lens = S.pack_reads(reads)
+        labels = np.zeros(len(reads), dtype=np.int32)
+        sp = np.array(span, dtype=np.uint8)
+        buf = C.create_string_buffer(1 << 16)
+        n = H.othost_consensus_cigars(S.ptr(bases), S.ptr(off), S.ptr(lens), S.ptr(sp), len(reads),
+                                      S.ptr(labels), 1, buf, len(buf))
+        return buf.raw[:n].decode().split("\n")[:-1]
+
+    first = run(["L", "0", "1", "2", "3"])      # the skipped member is read 0: first in plan order
+    assert len(first) == 4 and first[0] == ""   # nothing aligned before it in this fresh aligner
+    later = run(["0", "1", "L", "2", "3"])      # skipped member after an aligned one
+    assert len(later) == 4
+    k = [i for i, c in enumerate(later) if i > 0 and c == later[i - 1]]
+    assert k, later                              # it repeats its predecessor's CIGAR
