@@ -479,6 +479,38 @@ def run_extract(args, rank, world, local_rank):
                 e2e={"value": n * args.steps / t, "unit": "records/s",
                      "h2d_bytes_per_step": int(rec.nbytes + cig.nbytes + seq4.nbytes),
                      "d2h_bytes_per_step": int(len(bases) + begin.nbytes + status.nbytes + coords.nbytes + lens.nbytes)})
+    # ---- the hand-off to the alignment: every successfully extracted record of a region against
+    # every other one, (a) through the host (the extracted characters come back and go up again),
+    # (b) device to device (otgpu_region_edit_scores_extracted: only the tables cross PCIe) ----
+    okr = np.nonzero(status & 1)[0].astype(np.uint32)
+    per_region = np.bincount(okr // 60, minlength=n_regions).astype(np.uint64)
+    rs = np.zeros(n_regions + 1, dtype=np.uint32)
+    rs[1:] = np.cumsum(per_region)
+    npairs = per_region * (per_region - (per_region > 0)) // 2
+    so = np.zeros(n_regions, dtype=np.uint64)
+    so[1:] = np.cumsum(npairs[:-1])
+    n_sc = int(npairs.sum())
+    off_sel, len_sel = begin[:n][okr].copy(), lens[okr].copy()
+
+    def via_host():
+        st_, co_, le_, be_, ba_ = ctx.extract_reads(rec, cig, seq4)
+        return ctx.region_edit_scores(ba_, off_sel, len_sel, rs, so, n_sc)
+
+    def on_device():
+        ctx.extract_reads(rec, cig, seq4)
+        return ctx.region_edit_scores_extracted(okr, rs, so, n_sc)
+
+    chain = {}
+    for name, fn in (("via_host", via_host), ("device_resident", on_device)):
+        sc = fn()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            sc = fn()
+        chain[name] = {"ms_per_step": 1e3 * (time.perf_counter() - t0) / args.steps, "checksum": int(sc.astype(np.int64).sum())}
+    chain["identical"] = chain["via_host"]["checksum"] == chain["device_resident"]["checksum"]
+    chain["pairs"] = n_sc
+    chain["note"] = "extract + all-pairs edit distance per region; device_resident skips the H2D of the extracted bases"
+    line["extract_then_align"] = chain
     if not args.no_cpu_baseline:
         tr, out = reference(threads)
         mine = np.where(status & 1, lens.astype(np.int64), -1)

@@ -235,6 +235,19 @@ int otgpu_extract_reads(otgpu_ctx* ctx, const otgpu_bam_read* reads, uint32_t n_
                         uint64_t n_seq_bytes, uint8_t* status, int32_t* coords, uint32_t* out_len,
                         const char** bases, const uint64_t** begin);
 
+/* fill_dist_matrix over reads that the LAST otgpu_extract_reads call on ctx produced, without the
+ * round trip through the host: the extracted sequences stay on the device, and this call builds
+ * the alignment batch from them device to device (parse_alignment -> fill_dist_matrix,
+ * src/anseqs.cpp:431 -> src/analignments.cpp:117-124, with nothing but the tables crossing PCIe).
+ * read_index[r] = the extracted record that is read r of the batch (the caller keeps the records
+ * it wants: status, spanning flags, rq filter, coverage cap); region g owns reads
+ * [region_start[g], region_start[g+1]); scores as otgpu_region_edit_scores.
+ * OTGPU_ERR_STATE when ctx holds no extraction result. */
+int otgpu_region_edit_scores_extracted(otgpu_ctx* ctx, const uint32_t* read_index, uint32_t n_reads,
+                                       const uint32_t* region_start, uint32_t n_regions,
+                                       const uint64_t* score_off, uint64_t n_scores,
+                                       int32_t* scores_out);
+
 /* ---- kernel density estimates for the clustering cut ------------------------------------------ */
 /* KDE::f (reference src/ankde.cpp:9-23) as otter_find_clustering_dist uses it
  * (src/otterclust.cpp:20-29): for every region g the density of its pairwise distances

@@ -16,7 +16,7 @@ SYMBOLS = [
     "otgpu_batch_download", "otgpu_synchronize", "otgpu_last_align_ms", "otgpu_affine_cigars",
     "otgpu_edit_cigars", "otgpu_last_chunk_count", "otgpu_affine_cigars_packed",
     "otgpu_edit_cigars_packed", "otgpu_extract_reads", "otgpu_kde_densities",
-    "otgpu_region_edit_scores_hooked",
+    "otgpu_region_edit_scores_hooked", "otgpu_region_edit_scores_extracted",
 ]
 
 
@@ -87,6 +87,7 @@ def lib():
         l.otgpu_edit_scores.argtypes = [vp, vp, u64, vp, vp, u32, vp, u64, vp]
         l.otgpu_region_edit_scores.argtypes = [vp, vp, u64, vp, vp, u32, vp, u32, vp, u64, vp]
         l.otgpu_region_edit_scores_hooked.argtypes = [vp, vp, u64, vp, vp, u32, vp, u32, vp, u64, vp, vp]
+        l.otgpu_region_edit_scores_extracted.argtypes = [vp, vp, u32, vp, u32, vp, u64, vp]
         l.otgpu_batch_upload_regions.argtypes = [vp, vp, u64, vp, vp, u32, vp, u32, vp, u64]
         l.otgpu_batch_upload_pairs.argtypes = [vp, vp, u64, vp, vp, u32, vp, u64]
         l.otgpu_batch_align.argtypes = [vp]
@@ -198,6 +199,15 @@ class Context:
             self._h, _p(bases), C.c_uint64(bases.size), _p(off), _p(lens), C.c_uint32(len(lens)),
             _p(region_start), C.c_uint32(len(region_start) - 1), _p(score_off), C.c_uint64(n_scores),
             _p(out), C.byref(h)))
+        return out
+
+    def region_edit_scores_extracted(self, read_index, region_start, score_off, n_scores):
+        """fill_dist_matrix over records of the last extract_reads call, device to device."""
+        read_index = np.ascontiguousarray(read_index, dtype=np.uint32)
+        out = np.empty(n_scores, dtype=np.int32)
+        self._ck(self._l.otgpu_region_edit_scores_extracted(
+            self._h, _p(read_index), len(read_index), _p(region_start), len(region_start) - 1,
+            _p(score_off), n_scores, _p(out)))
         return out
 
     def last_chunk_count(self):

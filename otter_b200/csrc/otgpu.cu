@@ -258,6 +258,9 @@ struct otgpu_ctx {
   DevBuf aff_rings, aff_slab, aff_slab2, aff_ops, cigar_off, cigars, cigar_len;  // gap-affine path
   DevBuf cigar_begin, cigars_packed;            // packed CIGAR output (device side)
   DevBuf bam_reads, bam_cigar, bam_seq4, bam_status, bam_coords, bam_plan;  // read extraction
+  DevBuf bam_out, bam_begin, bam_len, gather_index;  // extracted reads, kept on the device
+  uint32_t extracted_reads = 0;              // records of the last otgpu_extract_reads call (0: none)
+  std::vector<uint32_t> extracted_len;       // their lengths (host copy)
   DevBuf kde_values, kde_off, kde_grid, kde_h, kde_inv_h, kde_out;          // density estimates
   void* h_cigars = nullptr;                     // pinned: packed CIGARs of the last call
   size_t h_cigars_cap = 0;
@@ -286,6 +289,7 @@ struct otgpu_ctx {
   otgpu_stats stats = {0, 0, 0, 0};
   cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // pack|expand|align|wide|end
   bool timed = false;
+  bool gather = false;  // upload_reads: the bases come from the device (k_gather_reads), not the host
 };
 
 namespace {
@@ -325,7 +329,7 @@ int next_pow2(int x) {
 // Shared front half of both upload flavours: reads + packed layout.
 int upload_reads(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const uint64_t* read_off,
                  const uint32_t* read_len, uint32_t n_reads) {
-  if (!ctx || (!bases && n_bases) || ((!read_off || !read_len) && n_reads)) return OTGPU_ERR_ARGS;
+  if (!ctx || (!bases && n_bases && !ctx->gather) || ((!read_off || !read_len) && n_reads)) return OTGPU_ERR_ARGS;
   CK(cudaSetDevice(ctx->device));
   // the previous batch (device buffers, pinned staging) must be finished before it is replaced
   CK(cudaStreamSynchronize(ctx->stream));
@@ -366,7 +370,7 @@ int upload_reads(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases, const u
   RS(read_flag, (size_t)n_reads * 4 + 4);
   RS(packed, (words + kPadBases / 16 + 4) * 4);
   RS(counters, sizeof(Counters));
-  if (n_bases)
+  if (n_bases && !ctx->gather)
     CK(cudaMemcpyAsync(static_cast<uint8_t*>(ctx->bases.p) + kPadBases, bases, n_bases,
                        cudaMemcpyHostToDevice, ctx->stream));
   if (n_reads) {
@@ -476,6 +480,7 @@ void otgpu_destroy(otgpu_ctx* ctx) {
                     &ctx->aff_slab, &ctx->aff_slab2, &ctx->aff_ops, &ctx->cigar_off, &ctx->cigars,
                     &ctx->cigar_len, &ctx->cigar_begin, &ctx->cigars_packed, &ctx->bam_reads,
                     &ctx->bam_cigar, &ctx->bam_seq4, &ctx->bam_status, &ctx->bam_coords, &ctx->bam_plan,
+                    &ctx->bam_out, &ctx->bam_begin, &ctx->bam_len, &ctx->gather_index,
                     &ctx->kde_values, &ctx->kde_off, &ctx->kde_grid, &ctx->kde_h, &ctx->kde_inv_h,
                     &ctx->kde_out};
   for (DevBuf* b : bufs)
@@ -1236,8 +1241,9 @@ extern "C" int otgpu_extract_reads(otgpu_ctx* ctx, const otgpu_bam_read* reads, 
   RS(bam_status, n_reads);
   RS(bam_coords, (size_t)n_reads * 8);
   RS(bam_plan, (size_t)n_reads * sizeof(ExtractPlan));
-  RS(cigar_len, (size_t)n_reads * 4);          // per-record output lengths (scan input)
-  RS(cigar_begin, ((size_t)n_reads + 1) * 8);  // start offsets
+  RS(bam_len, (size_t)n_reads * 4);            // per-record output lengths (scan input)
+  RS(bam_begin, ((size_t)n_reads + 1) * 8);    // start offsets
+  ctx->extracted_reads = 0;
   if (((size_t)n_reads + 1) * 8 > ctx->h_read_begin_cap) {
     if (ctx->h_read_begin) cudaFreeHost(ctx->h_read_begin);
     ctx->h_read_begin = nullptr;
@@ -1250,8 +1256,8 @@ extern "C" int otgpu_extract_reads(otgpu_ctx* ctx, const otgpu_bam_read* reads, 
   if (n_cigar_ops) CK(cudaMemcpyAsync(ctx->bam_cigar.p, cigar, n_cigar_ops * 4, cudaMemcpyHostToDevice, st));
   if (n_seq_bytes) CK(cudaMemcpyAsync(ctx->bam_seq4.p, seq4, n_seq_bytes, cudaMemcpyHostToDevice, st));
   const otgpu_bam_read* d_reads = static_cast<const otgpu_bam_read*>(ctx->bam_reads.p);
-  int32_t* d_len = static_cast<int32_t*>(ctx->cigar_len.p);
-  uint64_t* d_begin = static_cast<uint64_t*>(ctx->cigar_begin.p);
+  int32_t* d_len = static_cast<int32_t*>(ctx->bam_len.p);
+  uint64_t* d_begin = static_cast<uint64_t*>(ctx->bam_begin.p);
   ExtractPlan* d_plan = static_cast<ExtractPlan*>(ctx->bam_plan.p);
   k_bam_breakpoints<<<(n_reads + 255) / 256, 256, 0, st>>>(
       d_reads, n_reads, static_cast<const uint32_t*>(ctx->bam_cigar.p),
@@ -1265,7 +1271,7 @@ extern "C" int otgpu_extract_reads(otgpu_ctx* ctx, const otgpu_bam_read* reads, 
   CK(cudaMemcpyAsync(out_len, d_len, (size_t)n_reads * 4, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   const uint64_t total = static_cast<const uint64_t*>(ctx->h_read_begin)[n_reads];
-  RS(cigars_packed, total + 16);
+  RS(bam_out, total + 16);
   if (total + 1 > ctx->h_reads_cap) {
     if (ctx->h_reads) cudaFreeHost(ctx->h_reads);
     ctx->h_reads = nullptr;
@@ -1276,15 +1282,80 @@ extern "C" int otgpu_extract_reads(otgpu_ctx* ctx, const otgpu_bam_read* reads, 
   }
   if (total) {
     k_bam_decode<<<ctx->n_sm * 8, 256, 0, st>>>(d_reads, n_reads, static_cast<const uint8_t*>(ctx->bam_seq4.p),
-                                                d_plan, d_len, d_begin, static_cast<char*>(ctx->cigars_packed.p));
+                                                d_plan, d_len, d_begin, static_cast<char*>(ctx->bam_out.p));
     ctx->stats.kernel_launches++;
     CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(ctx->h_reads, ctx->cigars_packed.p, total, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(ctx->h_reads, ctx->bam_out.p, total, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
   }
   *bases = static_cast<const char*>(ctx->h_reads);
   *begin = static_cast<const uint64_t*>(ctx->h_read_begin);
+  // the extracted reads stay on the device for otgpu_region_edit_scores_extracted
+  try {
+    ctx->extracted_len.assign(out_len, out_len + n_reads);
+  } catch (...) {
+    return OTGPU_ERR_OOM;
+  }
+  ctx->extracted_reads = n_reads;
   return OTGPU_OK;
+}
+
+// Extracted reads -> the resident batch, device to device: read r of the batch is extracted record
+// index[r] (one CTA per read; HBM byte copy).
+__global__ void __launch_bounds__(128)
+k_gather_reads(const char* __restrict__ src, const uint64_t* __restrict__ begin,
+               const uint32_t* __restrict__ index, const uint64_t* __restrict__ read_off,
+               const uint32_t* __restrict__ read_len, uint8_t* __restrict__ bases) {
+  const uint32_t r = blockIdx.x;
+  const char* s = src + begin[index[r]];
+  uint8_t* d = bases + kPadBases + read_off[r];
+  for (uint32_t i = threadIdx.x; i < read_len[r]; i += blockDim.x) d[i] = (uint8_t)s[i];
+}
+
+extern "C" int otgpu_region_edit_scores_extracted(otgpu_ctx* ctx, const uint32_t* read_index,
+                                                  uint32_t n_reads, const uint32_t* region_start,
+                                                  uint32_t n_regions, const uint64_t* score_off,
+                                                  uint64_t n_scores, int32_t* scores_out) {
+  if (!ctx || (!read_index && n_reads) || !region_start || (!score_off && n_regions) ||
+      (!scores_out && n_scores))
+    return OTGPU_ERR_ARGS;
+  if (ctx->extracted_reads == 0) return OTGPU_ERR_STATE;  // no extraction result on the device
+  std::vector<uint64_t> off;
+  std::vector<uint32_t> len;
+  try {
+    off.resize(n_reads);
+    len.resize(n_reads);
+  } catch (...) {
+    return OTGPU_ERR_OOM;
+  }
+  uint64_t n_bases = 0;
+  for (uint32_t r = 0; r < n_reads; ++r) {
+    if (read_index[r] >= ctx->extracted_reads) return OTGPU_ERR_ARGS;
+    off[r] = n_bases;
+    len[r] = ctx->extracted_len[read_index[r]];
+    n_bases += len[r];
+  }
+  ctx->n_chunks_last = 1;
+  CK(cudaSetDevice(ctx->device));
+  // tables as for any region batch, but the bases never leave the device
+  ctx->gather = true;
+  int s = otgpu_batch_upload_regions(ctx, nullptr, n_bases, off.data(), len.data(), n_reads, region_start,
+                                     n_regions, score_off, n_scores);
+  ctx->gather = false;
+  if (s != OTGPU_OK) return s;
+  if (n_reads) {
+    RS(gather_index, (size_t)n_reads * 4);
+    CK(cudaMemcpyAsync(ctx->gather_index.p, read_index, (size_t)n_reads * 4, cudaMemcpyHostToDevice, ctx->stream));
+    k_gather_reads<<<n_reads, 128, 0, ctx->stream>>>(
+        static_cast<const char*>(ctx->bam_out.p), static_cast<const uint64_t*>(ctx->bam_begin.p),
+        static_cast<const uint32_t*>(ctx->gather_index.p), static_cast<const uint64_t*>(ctx->read_off.p),
+        static_cast<const uint32_t*>(ctx->read_len.p), static_cast<uint8_t*>(ctx->bases.p));
+    ctx->stats.kernel_launches++;
+    CK(cudaGetLastError());
+  }
+  s = otgpu_batch_align(ctx);
+  if (s == OTGPU_OK) s = otgpu_batch_download(ctx, scores_out, n_scores);
+  return s;
 }
 
 // ---- kernel density estimates (kde.cuh) ---------------------------------------------------------

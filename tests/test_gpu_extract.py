@@ -113,6 +113,43 @@ def test_extracted_reads_feed_the_distance_matrix(ctx):
     assert np.array_equal(got, want)
 
 
+def test_extracted_reads_stay_on_the_device(built):
+    """otgpu_extract_reads leaves its sequences on the device; otgpu_region_edit_scores_extracted
+    builds the alignment batch from them device to device: a subset of the records, in a different
+    order, over several regions (one empty), gives the scores of the same reads uploaded from the
+    host.  A CIGAR call in between must not disturb the extraction result; a context without one
+    refuses."""
+    import otter_b200
+    from otter_b200.capi import OtgpuError, PAIR_DTYPE
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "extract_golden.json")))["cases"]
+    rec, cig, seq4 = batch(gold)
+    with otter_b200.Context(0) as c:
+        with pytest.raises(OtgpuError):
+            c.region_edit_scores_extracted(np.zeros(2, np.uint32), np.array([0, 2], np.uint32),
+                                           np.array([0], np.uint64), 1)
+        status, coords, lens, begin, bases = c.extract_reads(rec, cig, seq4)
+        ok = [i for i, g in enumerate(gold) if g["ok"] and len(g["out"]) > 5]
+        rng = np.random.default_rng(5)
+        pick = rng.permutation(ok)[:60]
+        sizes = [9, 0, 14, 1, 20, 16]
+        rs = np.zeros(len(sizes) + 1, dtype=np.uint32)
+        rs[1:] = np.cumsum(sizes)
+        npairs = np.array([n * (n - 1) // 2 for n in sizes], dtype=np.uint64)
+        so = np.zeros(len(sizes), dtype=np.uint64)
+        so[1:] = np.cumsum(npairs[:-1])
+        # something else uses the context's CIGAR buffers in between
+        two = S.pack_reads([np.frombuffer(b"ACGTACGTAC", np.uint8), np.frombuffer(b"ACGTTCGTAC", np.uint8)])
+        c.cigars_packed(two[0], two[1], two[2], np.array([(0, 1, -1, 0, 0, 0)], dtype=PAIR_DTYPE))
+        got = c.region_edit_scores_extracted(pick[:int(rs[-1])], rs, so, int(npairs.sum()))
+        reads = [np.frombuffer(gold[i]["out"].encode(), dtype=np.uint8) for i in pick[:int(rs[-1])]]
+        hb, ho, hl = S.pack_reads(reads)
+        want = c.region_edit_scores(hb, ho, hl, rs, so, int(npairs.sum()))
+        assert np.array_equal(got, want)
+        with pytest.raises(OtgpuError):  # an index past the extracted records
+            c.region_edit_scores_extracted(np.array([len(gold) + 3, 0], np.uint32), np.array([0, 2], np.uint32),
+                                           np.array([0], np.uint64), 1)
+
+
 @pytest.mark.parametrize("omit", [0, 1])
 def test_read_extractor_host_layer(built, omit):
     """ReadExtractor (otter_b200/host/anseqs_b200.hpp): what parse_anreads keeps per region —
