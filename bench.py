@@ -963,6 +963,11 @@ def c4_strong(bench, args):
         dist.barrier(group=bench.gloo)
         if rank != 0:
             shm = shared_memory.SharedMemory(name=name)
+            try:  # rank 0 owns the segment: keep this process's resource tracker out of it
+                from multiprocessing import resource_tracker
+                resource_tracker.unregister(shm._name, "shared_memory")
+            except Exception:
+                pass
         full = np.ndarray((n_total,), dtype=np.int32, buffer=shm.buf)
     rows = full.reshape(n_regions, 435)
 

@@ -6,7 +6,7 @@ top-level function seen in address order."""
 import collections, csv, io, os, re, subprocess, sys, tempfile
 rep, lib = sys.argv[1], sys.argv[2]
 kern = sys.argv[3] if len(sys.argv) > 3 else "k_alignILi1024"
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 src = open(os.path.join(ROOT, "otter_b200/csrc/wfa_edit.cuh")).read().split("\n")
 # function extents of wfa_edit.cuh
 funcs = []
