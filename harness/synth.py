@@ -167,8 +167,11 @@ def c4s_batch(region_ids, procs=1):
         import multiprocessing as mp
         per = max(50, (len(region_ids) + 8 * procs - 1) // (8 * procs))
         chunks = [region_ids[i:i + per] for i in range(0, len(region_ids), per)]
-        with mp.get_context("fork").Pool(procs) as pool:
-            outs = pool.map(_c4s_pack, chunks)
+        try:  # (workers only run numpy; a stuck pool must not take the caller down with it)
+            with mp.get_context("fork").Pool(procs) as pool:
+                outs = pool.map_async(_c4s_pack, chunks).get(timeout=600)
+        except Exception:
+            outs = [_c4s_pack(c) for c in chunks]
     else:
         outs = [_c4s_pack(region_ids)]
     bases = np.concatenate([o[0] for o in outs]) if outs else np.zeros(0, np.uint8)

@@ -7,16 +7,20 @@ import collections, csv, io, os, re, subprocess, sys, tempfile
 rep, lib = sys.argv[1], sys.argv[2]
 kern = sys.argv[3] if len(sys.argv) > 3 else "k_alignILi1024"
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-src = open(os.path.join(ROOT, "otter_b200/csrc/wfa_edit.cuh")).read().split("\n")
-# function extents of wfa_edit.cuh
-funcs = []
-for i, l in enumerate(src, 1):
-    m = re.match(r"^(?:__device__|template|struct)?.*?\b([A-Za-z_0-9]+)\s*\((?:const|int|uint|unsigned|typename|Ring|Grp|otgpu)", l)
-    if l.startswith("__device__") and m:
-        funcs.append((i, m.group(1)))
-def func_of(line):
+# function extents of the kernel headers
+FILES = ["wfa_edit.cuh", "wfa_affine.cuh", "wfa_edit_cigar.cuh"]
+funcs = {}
+for fn in FILES:
+    src = open(os.path.join(ROOT, "otter_b200/csrc", fn)).read().split("\n")
+    fl = []
+    for i, l in enumerate(src, 1):
+        m = re.match(r"^(?:__device__|template|struct)?.*?\b([A-Za-z_0-9]+)\s*\((?:const|int|uint|unsigned|typename|Ring|Grp|otgpu|AffWork|AffSlot|EditJob|char)", l)
+        if l.startswith("__device__") and m:
+            fl.append((i, m.group(1)))
+    funcs[fn] = fl
+def func_of(fn, line):
     name = "?"
-    for a, n in funcs:
+    for a, n in funcs[fn]:
         if a <= line: name = n
         else: break
     return name
@@ -43,8 +47,8 @@ owner = "kernel"
 tot = ts = 0
 for r, (f, ln) in zip(body, tags):
     n, s = int(r[ie]), int(r[sm])
-    if f == "wfa_edit.cuh":
-        fn = func_of(ln)
+    if f in funcs:
+        fn = func_of(f, ln)
         if fn not in LEAF: owner = fn
         leaf = fn
     elif f == "otgpu.cu": owner = leaf = "kernel"
