@@ -228,30 +228,68 @@ __device__ int wfa_affine_pair(const AffWork& W, AffSlot* __restrict__ meta, con
       int32_t* o_d = RING_D(si);
       int mn[3] = {0x7fffffff, 0x7fffffff, 0x7fffffff};
       int mx[3] = {(int)0x80000000, (int)0x80000000, (int)0x80000000};
-      for (int kc = lo; kc <= hi; kc += 32) {
-        const int k = kc + lane;
-        if (k <= hi) {
-          const int ins_o = aff_rd(r_mo, mask, mo_lo, mo_hi, k - 1);
-          const int ins_e = aff_rd(r_ie, mask, ie_lo, ie_hi, k - 1);
-          const int del_o = aff_rd(r_mo, mask, mo_lo, mo_hi, k + 1);
-          const int del_e = aff_rd(r_de, mask, de_lo, de_hi, k + 1);
-          const bool i_ext = ins_e >= ins_o, d_ext = del_e >= del_o;  // ties prefer extend
-          const int ins = (i_ext ? ins_e : ins_o) + 1;
-          const int del = d_ext ? del_e : del_o;
-          const int mis = aff_rd(r_mm, mask, mm_lo, mm_hi, k) + 1;
-          int best = max(del, max(mis, ins));
-          int src = 0;
-          if (best == ins) src = 1;
-          if (best == del) src = 2;
-          if (best == mis) src = 0;  // last assignment wins: mismatch > deletion > insertion
-          if (has_i) o_i[k & mask] = ins;
-          if (has_d) o_d[k & mask] = del;
-          if (!in_bounds(best, k, plen, tlen)) best = kNull;
-          o_m[k & mask] = best;
-          W.slab[cells_top + (k - lo)] = (uint8_t)(src | (i_ext ? 4 : 0) | (d_ext ? 8 : 0));
-          if (best >= 0) { mn[0] = min(mn[0], k); mx[0] = max(mx[0], k); }
-          if (in_bounds(ins, k, plen, tlen)) { mn[1] = min(mn[1], k); mx[1] = max(mx[1], k); }
-          if (in_bounds(del, k, plen, tlen)) { mn[2] = min(mn[2], k); mx[2] = max(mx[2], k); }
+      // Two adjacent diagonals per lane, 64 per round (k0 even: one 64-bit access per ring and
+      // pair; twice the independent loads in flight per warp - this kernel waits on its ring
+      // round trips, not on issue slots: profiles/README.md r2m; 41.6 -> 38.1 ms per 11,800 C2
+      // alignments.  The same for the extend loop measured slower, 39.6 ms, and is not used).
+      for (int kc = lo & ~1; kc <= hi; kc += 64) {
+        const int k0 = kc + 2 * lane, k1 = k0 + 1;
+        if (k0 <= hi) {
+          const bool on0 = k0 >= lo, on1 = k1 <= hi;  // (kc may start one below lo; hi may be k0)
+          const int i0 = k0 & mask;                    // even: slots i0, i0+1 share an 8-byte word
+          // M[s-o-e] at k0-1 .. k0+2, I1[s-e] at k0-1, k0, D1[s-e] at k0+1, k0+2, M[s-x] at k0, k1
+          const int2 mo_p = *reinterpret_cast<const int2*>(r_mo + i0);
+          const int2 mm_p = *reinterpret_cast<const int2*>(r_mm + i0);
+          const int mo_m1 = aff_rd(r_mo, mask, mo_lo, mo_hi, k0 - 1);
+          const int mo_p2 = aff_rd(r_mo, mask, mo_lo, mo_hi, k0 + 2);
+          const int ie_m1 = aff_rd(r_ie, mask, ie_lo, ie_hi, k0 - 1);
+          const int ie_0 = aff_rd(r_ie, mask, ie_lo, ie_hi, k0);
+          const int de_p1 = aff_rd(r_de, mask, de_lo, de_hi, k0 + 1);
+          const int de_p2 = aff_rd(r_de, mask, de_lo, de_hi, k0 + 2);
+          const int mo_0 = (k0 >= mo_lo && k0 <= mo_hi) ? mo_p.x : kNull;
+          const int mo_1 = (k1 >= mo_lo && k1 <= mo_hi) ? mo_p.y : kNull;
+          const int mm_0 = (k0 >= mm_lo && k0 <= mm_hi) ? mm_p.x : kNull;
+          const int mm_1 = (k1 >= mm_lo && k1 <= mm_hi) ? mm_p.y : kNull;
+          // diagonal k0: ins from k0-1, del from k0+1; diagonal k1: ins from k0, del from k0+2
+          const bool ie0 = ie_m1 >= mo_m1, de0 = de_p1 >= mo_1;  // ties prefer extend
+          const bool ie1 = ie_0 >= mo_0, de1 = de_p2 >= mo_p2;
+          const int ins0 = (ie0 ? ie_m1 : mo_m1) + 1, del0 = de0 ? de_p1 : mo_1, mis0 = mm_0 + 1;
+          const int ins1 = (ie1 ? ie_0 : mo_0) + 1, del1 = de1 ? de_p2 : mo_p2, mis1 = mm_1 + 1;
+          int best0 = max(del0, max(mis0, ins0)), best1 = max(del1, max(mis1, ins1));
+          // mismatch > deletion > insertion on ties (:166-177)
+          const int src0 = best0 == mis0 ? 0 : (best0 == del0 ? 2 : 1);
+          const int src1 = best1 == mis1 ? 0 : (best1 == del1 ? 2 : 1);
+          if (!in_bounds(best0, k0, plen, tlen)) best0 = kNull;
+          if (!in_bounds(best1, k1, plen, tlen)) best1 = kNull;
+          const uint8_t c0 = (uint8_t)(src0 | (ie0 ? 4 : 0) | (de0 ? 8 : 0));
+          const uint8_t c1 = (uint8_t)(src1 | (ie1 ? 4 : 0) | (de1 ? 8 : 0));
+          if (on0 && on1) {
+            if (has_i) *reinterpret_cast<int2*>(o_i + i0) = make_int2(ins0, ins1);
+            if (has_d) *reinterpret_cast<int2*>(o_d + i0) = make_int2(del0, del1);
+            *reinterpret_cast<int2*>(o_m + i0) = make_int2(best0, best1);
+            W.slab[cells_top + (k0 - lo)] = c0;
+            W.slab[cells_top + (k1 - lo)] = c1;
+          } else if (on0) {
+            if (has_i) o_i[i0] = ins0;
+            if (has_d) o_d[i0] = del0;
+            o_m[i0] = best0;
+            W.slab[cells_top + (k0 - lo)] = c0;
+          } else if (on1) {
+            if (has_i) o_i[i0 + 1] = ins1;
+            if (has_d) o_d[i0 + 1] = del1;
+            o_m[i0 + 1] = best1;
+            W.slab[cells_top + (k1 - lo)] = c1;
+          }
+          if (on0) {
+            if (best0 >= 0) { mn[0] = min(mn[0], k0); mx[0] = max(mx[0], k0); }
+            if (in_bounds(ins0, k0, plen, tlen)) { mn[1] = min(mn[1], k0); mx[1] = max(mx[1], k0); }
+            if (in_bounds(del0, k0, plen, tlen)) { mn[2] = min(mn[2], k0); mx[2] = max(mx[2], k0); }
+          }
+          if (on1) {
+            if (best1 >= 0) { mn[0] = min(mn[0], k1); mx[0] = max(mx[0], k1); }
+            if (in_bounds(ins1, k1, plen, tlen)) { mn[1] = min(mn[1], k1); mx[1] = max(mx[1], k1); }
+            if (in_bounds(del1, k1, plen, tlen)) { mn[2] = min(mn[2], k1); mx[2] = max(mx[2], k1); }
+          }
         }
       }
       // trim each component to its first/last in-bounds diagonal (wavefront_compute.c:376-423)

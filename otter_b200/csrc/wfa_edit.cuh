@@ -188,19 +188,29 @@ struct EditJob {
 // with nothing to extend: they issue no loads).  All 32 lanes must call.
 // First window is unconditional; after that, private windows while several lanes are still
 // running, and once at most two are left each remaining run is finished by the whole warp.
+// In two halves, so that a caller with two diagonals per lane can issue both first windows before
+// the first vote: lcp_first = the unconditional first window (idle lanes, rem <= 0, probe position
+// 0 of both reads and discard the result), lcp_rest = private windows while several lanes are
+// still running, then each remaining run finished by the whole warp.  cont = this lane's run
+// matched its whole window and has more to compare.
 template <int BITS>
-__device__ __forceinline__ int lcp_warp(const EditJob& J, int v, int h, int rem, const int lane) {
+__device__ __forceinline__ int lcp_first(const EditJob& J, int v, int h, int rem, bool& cont) {
   constexpr int WIN = Pack<BITS>::kWin;
-  const bool on = rem > 0;  // idle lanes probe position 0 of both reads and discard the result
-  int m = match_window<BITS>(J.words, J.P, J.T, on ? v : 0, on ? h : 0);
-  int n = max(min(m, rem), 0);  // clamp at a sequence end (the reference stops on its sentinels)
-  bool cont = (m >= WIN) && (rem > WIN);
+  const bool on = rem > 0;
+  const int m = match_window<BITS>(J.words, J.P, J.T, on ? v : 0, on ? h : 0);
+  cont = (m >= WIN) && (rem > WIN);
+  return max(min(m, rem), 0);  // clamp at a sequence end (the reference stops on its sentinels)
+}
+template <int BITS>
+__device__ __forceinline__ int lcp_rest(const EditJob& J, int v, int h, int rem, int n, bool cont,
+                                        const int lane) {
+  constexpr int WIN = Pack<BITS>::kWin;
   unsigned pend = __ballot_sync(kFull, cont);
   if (pend == 0) return n;
   for (int it = 0;; ++it) {
     if (cont) {
       v += WIN; h += WIN; rem -= WIN;
-      m = match_window<BITS>(J.words, J.P, J.T, v, h);
+      const int m = match_window<BITS>(J.words, J.P, J.T, v, h);
       n += min(m, rem);
       cont = (m >= WIN) && (rem > WIN);
     }
@@ -236,6 +246,12 @@ __device__ __forceinline__ int lcp_warp(const EditJob& J, int v, int h, int rem,
     if (lane == src) n += got;
   }
   return n;
+}
+template <int BITS>
+__device__ __forceinline__ int lcp_warp(const EditJob& J, int v, int h, int rem, const int lane) {
+  bool cont;
+  const int n = lcp_first<BITS>(J, v, h, rem, cont);
+  return lcp_rest<BITS>(J, v, h, rem, n, cont, lane);
 }
 
 // A group of G lanes (the whole warp, or one of its halves) that works on one pair.  Every
