@@ -39,7 +39,8 @@ enum {
   OTGPU_ERR_NO_DEVICE = 2, /* no CUDA device / driver (there is no CPU fallback)              */
   OTGPU_ERR_CUDA = 3,      /* a CUDA call or kernel failed; see otgpu_last_cuda_error         */
   OTGPU_ERR_OOM = 4,       /* device or pinned-host allocation failed                         */
-  OTGPU_ERR_STATE = 5      /* call sequence error (e.g. align before upload)                  */
+  OTGPU_ERR_STATE = 5,     /* call sequence error (e.g. align before upload)                  */
+  OTGPU_ERR_LIMIT = 6      /* batch exceeds the fixed limits of otgpu_edit_scores_static      */
 };
 
 /* Score written for a pair whose wavefront became empty (WF_STATUS_UNFEASIBLE in
@@ -247,6 +248,34 @@ int otgpu_region_edit_scores_extracted(otgpu_ctx* ctx, const uint32_t* read_inde
                                        const uint32_t* region_start, uint32_t n_regions,
                                        const uint64_t* score_off, uint64_t n_scores,
                                        int32_t* scores_out);
+
+/* ---- edit-distance scores without any allocation --------------------------------------------- */
+/* No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same inputs, outputs and scores as otgpu_edit_scores, but no context and NO
+ * allocation of any kind (no cudaMalloc / cudaFree / cudaMallocHost, no stream or event creation):
+ * the staged batch (padded bases, 2-bit copy, tables, pair list, scores) and the alignment kernels'
+ * scratch (work-queue counters, heaviest-first order, overflow list, per-warp wavefront rings in
+ * HBM for the pairs that outgrow the shared-memory ring) live in ONE file-scope
+ * `static __device__ __align__(256)` array of OTGPU_STATIC_SCRATCH_BYTES (40 MiB), which every GPU
+ * that loads the library holds until the process exits.  Hence the fixed limits below; a larger
+ * batch is rejected with OTGPU_ERR_LIMIT before anything is launched.
+ *   device   CUDA device ordinal; stream   a cudaStream_t of that device, or NULL for the default
+ *   stream.  bases / read_off / read_len / pairs / scores_out: HOST buffers (pinned or pageable),
+ *   as for otgpu_edit_scores.  The call returns after the scores have arrived (it synchronises
+ *   `stream`).
+ * Every call on a device shares the one array, which keeps the last call's contents; the call
+ * clears what must start at zero itself.  Calls on the same device are serialised inside the
+ * library per process, but work that overlaps on the GPU through any other route (another process
+ * has its own copy; the same process cannot) would race: do not rely on the array between calls. */
+#define OTGPU_STATIC_MAX_BASES (4u << 20)   /* bytes of reads per call                          */
+#define OTGPU_STATIC_MAX_READS 4096u
+#define OTGPU_STATIC_MAX_PAIRS 131072u
+#define OTGPU_STATIC_MAX_READ_LEN 8192u     /* longest single read                              */
+#define OTGPU_STATIC_SCRATCH_BYTES (40u << 20)
+int otgpu_edit_scores_static(int device, void* stream, const uint8_t* bases, uint64_t n_bases,
+                             const uint64_t* read_off, const uint32_t* read_len, uint32_t n_reads,
+                             const otgpu_pair* pairs, uint64_t n_pairs, int32_t* scores_out);
 
 /* ---- kernel density estimates for the clustering cut ------------------------------------------ */
 /* KDE::f (reference src/ankde.cpp:9-23) as otter_find_clustering_dist uses it

@@ -20,6 +20,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -436,6 +437,9 @@ const char* otgpu_strerror(int status) {
     case OTGPU_ERR_CUDA: return "CUDA error";
     case OTGPU_ERR_OOM: return "out of memory";
     case OTGPU_ERR_STATE: return "call sequence error";
+    case OTGPU_ERR_LIMIT:
+      return "batch exceeds the fixed limits of otgpu_edit_scores_static (OTGPU_STATIC_MAX_* in "
+             "otter_b200.h: 4 MiB of bases, 4,096 reads, 131,072 pairs, reads of at most 8,192 bases)";
     default: return "unknown status";
   }
 }
@@ -1405,4 +1409,179 @@ extern "C" int otgpu_kde_densities(otgpu_ctx* ctx, const double* values, const u
   CK(cudaMemcpyAsync(densities_out, ctx->kde_out.p, (size_t)n_regions * n_grid * 8, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   return OTGPU_OK;
+}
+
+// ---- edit-distance scores without any allocation (otgpu_edit_scores_static) ----------------------
+// No counterpart in the reference; added for callers that
+// cannot call cudaMalloc.  The same kernels as otgpu_edit_scores (k_pack_reads, k_order_*,
+// k_align<1024>, k_align<0>), but the staged batch and all kernel scratch live in the file-scope
+// array below instead of the context's cudaMalloc'ed buffers.  In HOST code the array's name is
+// only a stand-in for the symbol: its device address is taken once per device with
+// cudaGetSymbolAddress (static_setup) and that pointer is what the kernels get.
+static __device__ __align__(256) unsigned char g_otgpu_static_scratch[OTGPU_STATIC_SCRATCH_BYTES];
+
+namespace {
+
+constexpr size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
+// layout of the array (byte offsets, each 256-byte aligned)
+constexpr size_t kStPackedWords = 2ull * (kPadBases / 16) + OTGPU_STATIC_MAX_BASES / 16 +
+                                  8ull * OTGPU_STATIC_MAX_READS + 8;  // per read <= len/16 + 8 words
+constexpr int kStWideCtas = 8;                                         // k_align<0> grid
+constexpr int kStWideCap = 32768;  // int32 per warp: next_pow2(2 * OTGPU_STATIC_MAX_READ_LEN + 256)
+constexpr size_t kStBases = 0;
+constexpr size_t kStPacked = kStBases + al256(2ull * kPadBases + OTGPU_STATIC_MAX_BASES + 16);
+constexpr size_t kStReadOff = kStPacked + al256(kStPackedWords * 4);
+constexpr size_t kStReadLen = kStReadOff + al256(8ull * OTGPU_STATIC_MAX_READS + 8);
+constexpr size_t kStPkOff = kStReadLen + al256(4ull * OTGPU_STATIC_MAX_READS + 4);
+constexpr size_t kStFlag = kStPkOff + al256(8ull * OTGPU_STATIC_MAX_READS + 8);
+constexpr size_t kStPairs = kStFlag + al256(4ull * OTGPU_STATIC_MAX_READS + 4);
+constexpr size_t kStScores = kStPairs + al256(sizeof(otgpu_pair) * (size_t)OTGPU_STATIC_MAX_PAIRS + 32);
+constexpr size_t kStOrder = kStScores + al256(4ull * OTGPU_STATIC_MAX_PAIRS + 4);
+constexpr size_t kStOvf = kStOrder + al256(4ull * OTGPU_STATIC_MAX_PAIRS + 4);
+constexpr size_t kStCounters = kStOvf + al256(4ull * OTGPU_STATIC_MAX_PAIRS + 4);
+constexpr size_t kStOrderCtl = kStCounters + al256(sizeof(Counters));
+constexpr size_t kStWide = kStOrderCtl + al256(sizeof(OrderCtl));
+constexpr size_t kStEnd = kStWide + al256((size_t)kStWideCtas * kWarpsPerCta * kStWideCap * 4);
+static_assert(kStEnd <= OTGPU_STATIC_SCRATCH_BYTES, "static scratch layout exceeds the array");
+static_assert(2 * OTGPU_STATIC_MAX_READ_LEN + 256 <= kStWideCap, "wide ring too small for the longest read");
+static_assert(OTGPU_STATIC_MAX_READ_LEN <= kMaxReadLen, "read length limit");
+
+struct StaticDev {
+  bool ready = false;
+  unsigned char* base = nullptr;  // device address of g_otgpu_static_scratch on this device
+  int n_sm = 0, grid_main = 0;
+};
+StaticDev g_static_dev[64];
+std::mutex g_static_mu[64];                              // one call at a time per device
+uint64_t g_static_pk[64][OTGPU_STATIC_MAX_READS + 1];    // host: packed-word offsets of the call
+
+#define CKS(call)                                         \
+  do {                                                    \
+    if ((call) != cudaSuccess) {                          \
+      cudaGetLastError();                                 \
+      return OTGPU_ERR_CUDA;                              \
+    }                                                     \
+  } while (0)
+
+// Once per device, with that device current.
+int static_setup(int device, StaticDev& d) {
+  if (d.ready) return OTGPU_OK;
+  void* p = nullptr;
+  CKS(cudaGetSymbolAddress(&p, g_otgpu_static_scratch));
+  if (!p) return OTGPU_ERR_CUDA;
+  CKS(cudaDeviceGetAttribute(&d.n_sm, cudaDevAttrMultiProcessorCount, device));
+  int per_sm = 0;
+  CKS(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_align<1024>, kCtaThreads, ring_bytes(1024)));
+  if (per_sm < 1) per_sm = 1;
+  d.grid_main = d.n_sm * per_sm;
+  d.base = static_cast<unsigned char*>(p);
+  d.ready = true;
+  return OTGPU_OK;
+}
+
+int static_run(int device, cudaStream_t st, const uint8_t* bases, uint64_t n_bases, const uint64_t* read_off,
+               const uint32_t* read_len, uint32_t n_reads, const otgpu_pair* pairs, uint64_t n_pairs,
+               int32_t* scores_out) {
+  StaticDev& d = g_static_dev[device];
+  if (int s = static_setup(device, d)) return s;
+  unsigned char* S = d.base;
+  // packed layout, as upload_reads does it: guard words either side, reads 16-byte aligned
+  uint64_t* pk = g_static_pk[device];
+  uint64_t words = kPadBases / 16;
+  uint32_t max_len = 0;
+  for (uint32_t r = 0; r < n_reads; ++r) {
+    pk[r] = words;
+    words += (((uint64_t)read_len[r] + 15) / 16 + 2 + 3) & ~3ull;
+    if (read_len[r] > max_len) max_len = read_len[r];
+  }
+  if (words + kPadBases / 16 + 4 > kStPackedWords) return OTGPU_ERR_LIMIT;  // (cannot happen within the limits)
+  DevBatch b;
+  b.bases = S + kStBases;
+  b.read_off = reinterpret_cast<const uint64_t*>(S + kStReadOff);
+  b.read_len = reinterpret_cast<const uint32_t*>(S + kStReadLen);
+  b.pk_off = reinterpret_cast<const uint64_t*>(S + kStPkOff);
+  b.packed = reinterpret_cast<const uint32_t*>(S + kStPacked);
+  b.read_flag = reinterpret_cast<uint32_t*>(S + kStFlag);
+  b.pairs = reinterpret_cast<const otgpu_pair*>(S + kStPairs);
+  b.scores = reinterpret_cast<int32_t*>(S + kStScores);
+  b.n_pairs = n_pairs;
+  b.n_reads = n_reads;
+  Counters* ctr = reinterpret_cast<Counters*>(S + kStCounters);
+  OrderCtl* ctl = reinterpret_cast<OrderCtl*>(S + kStOrderCtl);
+  uint32_t* order = reinterpret_cast<uint32_t*>(S + kStOrder);
+  uint32_t* ovf = reinterpret_cast<uint32_t*>(S + kStOvf);
+  int32_t* wide = reinterpret_cast<int32_t*>(S + kStWide);
+  // inputs into the array (its guard regions keep whatever they held: their content is never used)
+  if (n_bases) CKS(cudaMemcpyAsync(S + kStBases + kPadBases, bases, n_bases, cudaMemcpyHostToDevice, st));
+  CKS(cudaMemcpyAsync(S + kStReadOff, read_off, (size_t)n_reads * 8, cudaMemcpyHostToDevice, st));
+  CKS(cudaMemcpyAsync(S + kStReadLen, read_len, (size_t)n_reads * 4, cudaMemcpyHostToDevice, st));
+  CKS(cudaMemcpyAsync(S + kStPkOff, pk, (size_t)n_reads * 8, cudaMemcpyHostToDevice, st));
+  CKS(cudaMemcpyAsync(S + kStPairs, pairs, (size_t)n_pairs * sizeof(otgpu_pair), cudaMemcpyHostToDevice, st));
+  // what must start at zero: the array keeps the last call's contents
+  CKS(cudaMemsetAsync(ctr, 0, sizeof(Counters), st));
+  CKS(cudaMemsetAsync(ctl, 0, sizeof(OrderCtl), st));
+  CKS(cudaMemsetAsync(b.read_flag, 0, (size_t)n_reads * 4, st));
+#ifdef OTGPU_CHECK_BOUNDS
+  {
+    CheckRange r[2];
+    r[0].lo = b.packed;
+    r[0].hi = b.packed + kStPackedWords;
+    r[1].lo = reinterpret_cast<const uint32_t*>(S + kStBases);
+    r[1].hi = r[1].lo + (kStPacked - kStBases) / 4;
+    CKS(cudaMemcpyToSymbolAsync(otgpu_check_range, r, sizeof r, 0, cudaMemcpyHostToDevice, st));
+  }
+#endif
+  k_pack_reads<<<n_reads, 128, 0, st>>>(b, reinterpret_cast<uint32_t*>(S + kStPacked));
+  const int g = (int)((n_pairs + 255) / 256 < (uint64_t)d.n_sm * 8 ? (n_pairs + 255) / 256 : (uint64_t)d.n_sm * 8);
+  k_order_count<<<g, 256, 0, st>>>(b.pairs, n_pairs, b.read_len, ctl);
+  k_order_scan<<<1, 1, 0, st>>>(ctl);
+  k_order_scatter<<<g, 256, 0, st>>>(b.pairs, n_pairs, b.read_len, ctl, order);
+  // 1024-slot shared ring for every pair; the ones that outgrow it finish on the HBM rings
+  int wide_cap = next_pow2(2 * (int)max_len + 256);
+  if (wide_cap > kStWideCap) return OTGPU_ERR_LIMIT;
+  k_align<1024><<<d.grid_main, kCtaThreads, ring_bytes(1024), st>>>(b, ctr, order, -1, 0, ovf, nullptr, wide_cap);
+  k_align<0><<<kStWideCtas, kCtaThreads, 0, st>>>(b, ctr, ovf, 1, 2, ovf, wide, wide_cap);
+  CKS(cudaGetLastError());
+  CKS(cudaMemcpyAsync(scores_out, b.scores, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, st));
+  CKS(cudaStreamSynchronize(st));
+  return OTGPU_OK;
+}
+
+}  // namespace
+
+extern "C" int otgpu_edit_scores_static(int device, void* stream, const uint8_t* bases, uint64_t n_bases,
+                                        const uint64_t* read_off, const uint32_t* read_len,
+                                        uint32_t n_reads, const otgpu_pair* pairs, uint64_t n_pairs,
+                                        int32_t* scores_out) {
+  if ((!bases && n_bases) || ((!read_off || !read_len) && n_reads) || (!pairs && n_pairs) ||
+      (!scores_out && n_pairs))
+    return OTGPU_ERR_ARGS;
+  // the fixed limits of the static array come first: nothing is launched for a batch beyond them
+  if (n_bases > OTGPU_STATIC_MAX_BASES || n_reads > OTGPU_STATIC_MAX_READS || n_pairs > OTGPU_STATIC_MAX_PAIRS)
+    return OTGPU_ERR_LIMIT;
+  for (uint32_t r = 0; r < n_reads; ++r) {
+    if (read_len[r] > OTGPU_STATIC_MAX_READ_LEN) return OTGPU_ERR_LIMIT;
+    if (read_off[r] + read_len[r] > n_bases) return OTGPU_ERR_ARGS;
+  }
+  for (uint64_t i = 0; i < n_pairs; ++i) {  // as otgpu_batch_upload_pairs
+    const otgpu_pair& p = pairs[i];
+    if (p.pattern >= n_reads || p.text >= n_reads) return OTGPU_ERR_ARGS;
+    if (p.pattern_begin_free >= 0) {
+      if (p.pattern_end_free < 0 || p.text_begin_free < 0 || p.text_end_free < 0 ||
+          (uint32_t)p.pattern_begin_free > read_len[p.pattern] ||
+          (uint32_t)p.pattern_end_free > read_len[p.pattern] ||
+          (uint32_t)p.text_begin_free > read_len[p.text] || (uint32_t)p.text_end_free > read_len[p.text])
+        return OTGPU_ERR_ARGS;
+    }
+  }
+  if (device < 0 || device >= 64 || device >= otgpu_device_count()) return OTGPU_ERR_NO_DEVICE;
+  if (n_pairs == 0) return OTGPU_OK;
+  std::lock_guard<std::mutex> lk(g_static_mu[device]);
+  int prev = -1;
+  if (cudaGetDevice(&prev) != cudaSuccess) { cudaGetLastError(); return OTGPU_ERR_CUDA; }
+  if (cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); return OTGPU_ERR_CUDA; }
+  const int s = static_run(device, static_cast<cudaStream_t>(stream), bases, n_bases, read_off, read_len,
+                           n_reads, pairs, n_pairs, scores_out);
+  if (prev >= 0 && prev != device) cudaSetDevice(prev);
+  return s;
 }
