@@ -317,20 +317,66 @@ __device__ __forceinline__ uint32_t first_diff(const EditJob& J, int v, int h) {
   return bit >> Pack<BITS>::kLogBits;
 }
 
+// The same over a 128-bit window (four words per read: 63 compared bases at 2 bit, 15 at 8 bit, the
+// last base again a sentinel difference): continuation of a run that outlived its first window.
+// Touches up to four words past the word holding the position (buffers carry guards for that).
+template <int BITS>
+__device__ __forceinline__ uint32_t first_diff_wide(const EditJob& J, int v, int h) {
+  uint32_t x[4];
+  {
+    const int a = (BITS == 2) ? v : J.P.sh0 + v, b = (BITS == 2) ? h : J.T.sh0 + h;
+    const uint32_t* p = J.words + (J.P.word0 + (uint32_t)(a >> Pack<BITS>::kLogBpw));
+    const uint32_t* t = J.words + (J.T.word0 + (uint32_t)(b >> Pack<BITS>::kLogBpw));
+#ifdef OTGPU_CHECK_BOUNDS
+    {
+      const CheckRange r0 = otgpu_check_range[0], r1 = otgpu_check_range[1];
+      const bool okp = (p >= r0.lo && p + 5 <= r0.hi) || (p >= r1.lo && p + 5 <= r1.hi);
+      const bool okt = (t >= r0.lo && t + 5 <= r0.hi) || (t >= r1.lo && t + 5 <= r1.hi);
+      if (!okp || !okt) {
+        atomicAdd(&otgpu_check_oob, 1ull);
+        p = t = r0.lo;
+      }
+      if ((threadIdx.x & 31) == 0) atomicAdd(&otgpu_check_loads, 2ull);
+    }
+#endif
+    const uint32_t p0 = __ldg(p), p1 = __ldg(p + 1), p2 = __ldg(p + 2), p3 = __ldg(p + 3), p4 = __ldg(p + 4);
+    const uint32_t t0 = __ldg(t), t1 = __ldg(t + 1), t2 = __ldg(t + 2), t3 = __ldg(t + 3), t4 = __ldg(t + 4);
+    const int sp = a << Pack<BITS>::kLogBits, st = b << Pack<BITS>::kLogBits;
+    x[0] = __funnelshift_r(p0, p1, sp) ^ __funnelshift_r(t0, t1, st);
+    x[1] = __funnelshift_r(p1, p2, sp) ^ __funnelshift_r(t1, t2, st);
+    x[2] = __funnelshift_r(p2, p3, sp) ^ __funnelshift_r(t2, t3, st);
+    x[3] = (__funnelshift_r(p3, p4, sp) ^ __funnelshift_r(t3, t4, st)) | 0x80000000u;
+  }
+  const uint32_t lo2 = x[0] | x[1];
+  const uint32_t sel = lo2 ? (x[0] ? x[0] : x[1]) : (x[2] ? x[2] : x[3]);
+  const uint32_t word = lo2 ? (x[0] ? 0u : 32u) : (x[2] ? 64u : 96u);
+  return ((uint32_t)(__ffs(sel) - 1) + word) >> Pack<BITS>::kLogBits;
+}
+
 // Slow path of a pass: some lane's first window matched completely.  n = bases matched so far
 // from (v,h), rem = the limit, c = this lane's run is still pending.  A few rounds of private
 // windows, then every run still pending is finished by the whole group.  Returns the new n.
-template <int BITS, int G>
+template <int BITS, int G, bool WIDE_ALL = false>
 __device__ __forceinline__ int lcp_more(const EditJob& J, const Grp<G>& g, int v, int h, int rem,
                                         bool c, int n) {
-  constexpr int WE = Pack<BITS>::kWin - 1;
+  // the first continuation window is 64 bits (most runs of noisy reads end inside it), the later
+  // ones 128 bits (63 bases at 2 bit: a long run of low-error reads needs half the iterations).
+  // WIDE_ALL (every ring but the 1024-slot one, i.e. long reads and overflow pairs): 128 bits from the start - measured on C3, and the
+  // two-flavour loop costs that kernel spills.  C1 25.3 -> 24.8 ms, C2/300 87.5 -> 86.9, C3/60 ~94 -> 91.
+  constexpr int WE = Pack<BITS>::kWin - 1, WE2 = 2 * Pack<BITS>::kWin - 1;
   unsigned pend;
   for (int it = 0;; ++it) {
     if (c) {
       const int left = rem - n;
-      const uint32_t fd = first_diff<BITS>(J, v + n, h + n);
-      n += (int)min(fd, (uint32_t)left);
-      c = fd == (uint32_t)WE && left > WE;
+      if (!WIDE_ALL && it == 0) {
+        const uint32_t fd = first_diff<BITS>(J, v + n, h + n);
+        n += (int)min(fd, (uint32_t)left);
+        c = fd == (uint32_t)WE && left > WE;
+      } else {
+        const uint32_t fd = first_diff_wide<BITS>(J, v + n, h + n);
+        n += (int)min(fd, (uint32_t)left);
+        c = fd == (uint32_t)WE2 && left > WE2;
+      }
     }
     pend = __ballot_sync(g.mask, c);
     if (pend == 0) return n;
@@ -439,10 +485,10 @@ __device__ __forceinline__ void wf_pass(const Ring<CAP>& R, const EditJob& J, co
       if (__any_sync(g.mask, (n0 == WE) | (n1 == WE))) {
         const bool c0 = ok0 && n0 == WE && rem0 > WE, c1 = ok1 && n1 == WE && rem1 > WE;
         if (__any_sync(g.mask, c0 | c1)) {  // each lane finishes one pending run per call
-          const int n = lcp_more<BITS, G>(J, g, c0 ? v0 : v1, c0 ? m0 : m1, c0 ? rem0 : rem1, c0 | c1,
+          const int n = lcp_more<BITS, G, CAP != 1024>(J, g, c0 ? v0 : v1, c0 ? m0 : m1, c0 ? rem0 : rem1, c0 | c1,
                                           c0 ? n0 : n1);
           if (c0) n0 = n; else n1 = n;
-          if (__any_sync(g.mask, c0 & c1)) n1 = lcp_more<BITS, G>(J, g, v1, m1, rem1, c0 & c1, n1);
+          if (__any_sync(g.mask, c0 & c1)) n1 = lcp_more<BITS, G, CAP != 1024>(J, g, v1, m1, rem1, c0 & c1, n1);
         }
       }
       m0 += n0;
@@ -482,7 +528,7 @@ __device__ __forceinline__ void wf_pass(const Ring<CAP>& R, const EditJob& J, co
       int n = (int)min(first_diff<BITS>(J, v, m), (uint32_t)rem);
       if (__any_sync(g.mask, n == WE)) {
         const bool c = ok && n == WE && rem > WE;
-        if (__any_sync(g.mask, c)) n = lcp_more<BITS, G>(J, g, v, m, rem, c, n);
+        if (__any_sync(g.mask, c)) n = lcp_more<BITS, G, CAP != 1024>(J, g, v, m, rem, c, n);
       }
       m += n;
       if (EF) fin |= ok && ((tr - n <= 0 && pr - n <= J.pe) || (pr - n <= 0 && tr - n <= J.te));
@@ -684,7 +730,7 @@ __device__ __forceinline__ int wf_narrow_run(const Ring<CAP>& R, const EditJob& 
     int n = (int)min(first_diff<BITS>(J, v, m), (uint32_t)rem);
     if (__any_sync(kFull, n == WE)) {
       const bool c = ok && n == WE && rem > WE;
-      if (__any_sync(kFull, c)) n = lcp_more<BITS, 32>(J, Grp<32>(lane), v, m, rem, c, n);
+      if (__any_sync(kFull, c)) n = lcp_more<BITS, 32, CAP != 1024>(J, Grp<32>(lane), v, m, rem, c, n);
     }
     bool fin = false;
     if (EF) fin = ok && ((tr - n <= 0 && pr - n <= J.pe) || (pr - n <= 0 && tr - n <= J.te));

@@ -130,3 +130,24 @@ def test_distmatrix_index_matches_reference_layout():
                 assert ((2 * n - 3 - i) * i >> 1) + j - 1 == q
                 assert i * (2 * n - i - 1) // 2 + (j - i - 1) == q  # k_expand_regions' formula
                 q += 1
+
+
+def test_static_entry_point_checks_its_limits_before_any_device_work(built):
+    """otgpu_edit_scores_static rejects a batch beyond its fixed limits with OTGPU_ERR_LIMIT (6) and a
+    message that names them, before it looks for a device - so this holds on a CPU-only box too."""
+    import numpy as np
+    import otter_b200
+    from otter_b200.capi import PAIR_DTYPE
+    l = otter_b200.lib()
+    vp = C.c_void_p
+    bases = np.full(9000 + 100, ord("A"), dtype=np.uint8)
+    off = np.array([0, 9000], dtype=np.uint64)
+    lens = np.array([9000, 100], dtype=np.uint32)      # first read longer than 8,192
+    pairs = np.array([(0, 1, -1, 0, 0, 0)], dtype=PAIR_DTYPE)
+    out = np.zeros(1, dtype=np.int32)
+    st = l.otgpu_edit_scores_static(0, None, bases.ctypes.data_as(vp), C.c_uint64(bases.size),
+                                    off.ctypes.data_as(vp), lens.ctypes.data_as(vp), C.c_uint32(2),
+                                    pairs.ctypes.data_as(vp), C.c_uint64(1), out.ctypes.data_as(vp))
+    assert st == 6
+    msg = l.otgpu_strerror(st)
+    assert b"fixed limits" in msg and b"8,192" in msg
