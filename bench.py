@@ -948,9 +948,22 @@ def c4_strong(bench, args):
 
     # Host-side gather (one box): a shared-memory array of all the scores in description order;
     # every rank places its shard's rows, a gloo barrier closes the step.  No device collective.
+    # Where /dev/shm is too small for the array (a SIGBUS otherwise), rank 0 collects the shards with
+    # a gloo gather instead.
     shm = None
-    if world == 1:
-        full = np.empty(n_total, dtype=np.int32)
+    use_shm = world > 1
+    if world > 1:
+        try:
+            vfs = os.statvfs("/dev/shm")
+            use_shm = vfs.f_bavail * vfs.f_frsize > 4 * n_total + (64 << 20) and \
+                not os.environ.get("OTB200_NO_SHM")  # (switch: exercise the fallback)
+        except OSError:
+            use_shm = False
+        flag = torch.tensor([1 if use_shm else 0], dtype=torch.int32)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=bench.gloo)  # every rank must agree
+        use_shm = bool(flag.item())
+    if not use_shm:
+        full = np.empty(n_total, dtype=np.int32) if rank == 0 else None
     else:
         from multiprocessing import shared_memory
         name = f"otb200_c4_{os.environ.get('MASTER_PORT', '0')}"
@@ -969,13 +982,22 @@ def c4_strong(bench, args):
             except Exception:
                 pass
         full = np.ndarray((n_total,), dtype=np.int32, buffer=shm.buf)
-    rows = full.reshape(n_regions, 435)
+    rows = full.reshape(n_regions, 435) if full is not None else None
 
     def gather(scores):
-        rows[mine] = scores.reshape(-1, 435)
-        if world > 1:
-            dist.barrier(group=bench.gloo)
-        return full
+        if world == 1 or use_shm:
+            rows[mine] = scores.reshape(-1, 435)
+            if world > 1:
+                dist.barrier(group=bench.gloo)
+            return
+        t = torch.from_numpy(scores)
+        if rank == 0:
+            bufs = [torch.empty(435 * len(sh), dtype=torch.int32) for sh in shards]
+            dist.gather(t, bufs, dst=0, group=bench.gloo)
+            for sh, buf in zip(shards, bufs):
+                rows[sh] = buf.numpy().reshape(-1, 435)
+        else:
+            dist.gather(t, None, dst=0, group=bench.gloo)
 
     bench.e2e_step(B, pin)  # warm-up (first touch of the device buffers)
     gather(pin["out"].array)
@@ -1030,7 +1052,8 @@ def c4_strong(bench, args):
             rec["limiter"] = lim
         dist.barrier(group=bench.gloo)
     if rank == 0:
-        rec["gather"] = "shared-memory array on the host, every rank places its shard's rows; gloo barrier" \
+        rec["gather"] = ("shared-memory array on the host, every rank places its shard's rows; gloo barrier"
+                         if use_shm else "gloo gather to rank 0 (/dev/shm too small for the array)") \
             if world > 1 else "local placement"
     if rank == 0 and not args.no_cpu_baseline:
         # spot check against the unmodified reference: the first regions of the description
