@@ -101,6 +101,8 @@ double now_s() {
   return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 thread_local FillTimes g_last_fill = {0, 0, 0, 0, 0};
+// how many fill_dist_matrices calls fill_dist_matrices_multi is about to run side by side
+std::atomic<int> g_fill_shares{1};
 
 // Producer side of the hooked C-ABI call: worker threads copy the reads into the pinned staging
 // buffer front to back and publish how far they got; the library waits for the bytes of a chunk
@@ -183,7 +185,10 @@ void fill_dist_matrices_multi(const bool& ignore_haps, std::vector<wfa::WFAligne
   const std::vector<int> part = partition_regions_by_work(jobs, (int)aligners.size());
   std::vector<std::vector<RegionDistJob>> share(aligners.size());
   for (size_t g = 0; g < jobs.size(); ++g) share[part[g]].push_back(jobs[g]);
-  // one host thread per device; the staging buffers are per thread, the contexts per aligner
+  // one host thread per device; staging buffers and contexts are per aligner
+  int n_shares = 0;
+  for (const auto& sh : share) n_shares += !sh.empty();
+  g_fill_shares.store(std::max(1, n_shares), std::memory_order_relaxed);
   std::vector<std::thread> pool;
   for (size_t d = 1; d < aligners.size(); ++d)
     if (!share[d].empty())
@@ -196,6 +201,7 @@ void fill_dist_matrices_multi(const bool& ignore_haps, std::vector<wfa::WFAligne
     if (times) (*times)[0] = last_fill_times();
   }
   for (auto& th : pool) th.join();
+  g_fill_shares.store(1, std::memory_order_relaxed);
 }
 
 void fill_dist_matrices(const bool& ignore_haps, wfa::WFAligner& aligner,
@@ -243,7 +249,23 @@ void fill_dist_matrices(const bool& ignore_haps, wfa::WFAligner& aligner,
   // The copy into pinned staging is the longest host step of a wave.  Worker threads run it front
   // to back and publish a watermark; in the all-spanning case (below) the device call starts at
   // once and waits, chunk by chunk, only for the bytes it is about to upload.
-  const int workers = total > ((size_t)8 << 20) ? 6 : 1;
+  // Up to 6 copy threads per call, fewer when several calls run at once (fill_dist_matrices_multi:
+  // one call per device): with 8 devices on 32 cores, 8 x (6 + 1) threads oversubscribe the host
+  // and the slowest share waits for its copy (profiles/README.md r2v: 15 of 52 ms).
+  struct InFlight {
+    std::atomic<int>& n;
+    explicit InFlight(std::atomic<int>& c) : n(c) { n.fetch_add(1, std::memory_order_relaxed); }
+    ~InFlight() { n.fetch_sub(1, std::memory_order_relaxed); }
+  };
+  static std::atomic<int> calls_in_flight{0};
+  const InFlight in_flight(calls_in_flight);
+  int workers = 1;
+  if (total > ((size_t)8 << 20)) {
+    const int hw = (int)std::thread::hardware_concurrency();
+    const int sharing = std::max(g_fill_shares.load(std::memory_order_relaxed),
+                                 calls_in_flight.load(std::memory_order_relaxed));
+    workers = std::min(6, std::max(2, (hw > 0 ? hw : 8) / sharing - 1));
+  }
   const size_t n_seqs = seqs.size();
   constexpr size_t kBlock = 64;  // reads per unit of work
   const size_t n_blocks = (n_seqs + kBlock - 1) / kBlock;
