@@ -249,6 +249,40 @@ int otgpu_region_edit_scores_extracted(otgpu_ctx* ctx, const uint32_t* read_inde
                                        const uint64_t* score_off, uint64_t n_scores,
                                        int32_t* scores_out);
 
+/* ---- partial-order consensus ------------------------------------------------------------------ */
+/* otter's PPOA (reference src/anppoa.hpp:63-369, as rapid_consensus drives it,
+ * src/analignments.cpp:258-290) for many alleles at once, one warp per graph: the backbone read
+ * seeds the graph (init :63-83), every member is threaded through it along its CIGAR over
+ * (backbone = pattern, member = text) with its spanning flags (insert_alignment :112-233), edge
+ * weights are damped with (c, t) (adjust_weights :235-244) and the consensus is the heaviest path
+ * into an ending node (consensus :305-369).  Byte-identical to the reference's string.
+ *   graphs[g]   backbone read, its members [first_member, first_member + n_members), c and t;
+ *   members[m]  read index, flags (bit0 is_spanning_l, bit1 is_spanning_r), CIGAR = cigars[cigar_off
+ *               .. cigar_off + cigar_len) over the characters M X I D.
+ * consensus_len[g] = length of graph g's consensus (may be 0: the caller substitutes "N" as the
+ * reference does, src/analignments.cpp:290); the strings themselves are packed end to end in
+ * memory the context owns (valid until the next call on ctx): graph g at
+ * (*consensus)[(*begin)[g] .. (*begin)[g] + consensus_len[g]). */
+typedef struct {
+  uint32_t backbone;
+  uint32_t first_member;
+  uint32_t n_members;
+  float c, t;
+} otgpu_ppoa_graph;
+typedef struct {
+  uint32_t read;
+  uint32_t flags;
+  uint64_t cigar_off;
+  uint32_t cigar_len;
+  uint32_t reserved;
+} otgpu_ppoa_member;
+int otgpu_ppoa_consensus(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                         const uint64_t* read_off, const uint32_t* read_len, uint32_t n_reads,
+                         const otgpu_ppoa_graph* graphs, uint32_t n_graphs,
+                         const otgpu_ppoa_member* members, uint32_t n_members, const char* cigars,
+                         uint64_t n_cigar_bytes, int32_t* consensus_len, const char** consensus,
+                         const uint64_t** begin);
+
 /* ---- edit-distance scores without any allocation --------------------------------------------- */
 /* No counterpart in the reference: added for callers that
  * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that

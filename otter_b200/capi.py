@@ -17,7 +17,7 @@ SYMBOLS = [
     "otgpu_edit_cigars", "otgpu_last_chunk_count", "otgpu_affine_cigars_packed",
     "otgpu_edit_cigars_packed", "otgpu_extract_reads", "otgpu_kde_densities",
     "otgpu_region_edit_scores_hooked", "otgpu_region_edit_scores_extracted",
-    "otgpu_edit_scores_static",
+    "otgpu_edit_scores_static", "otgpu_ppoa_consensus",
 ]
 
 
@@ -90,6 +90,7 @@ def lib():
         l.otgpu_region_edit_scores_hooked.argtypes = [vp, vp, u64, vp, vp, u32, vp, u32, vp, u64, vp, vp]
         l.otgpu_region_edit_scores_extracted.argtypes = [vp, vp, u32, vp, u32, vp, u64, vp]
         l.otgpu_edit_scores_static.argtypes = [i32, vp, vp, u64, vp, vp, u32, vp, u64, vp]
+        l.otgpu_ppoa_consensus.argtypes = [vp, vp, u64, vp, vp, u32, vp, u32, vp, u32, vp, u64, vp, vp, vp]
         l.otgpu_batch_upload_regions.argtypes = [vp, vp, u64, vp, vp, u32, vp, u32, vp, u64]
         l.otgpu_batch_upload_pairs.argtypes = [vp, vp, u64, vp, vp, u32, vp, u64]
         l.otgpu_batch_align.argtypes = [vp]

@@ -15,7 +15,9 @@
 #include "wfa_edit_cigar.cuh"
 #include "bam_extract.cuh"
 #include "kde.cuh"
+#include "ppoa.cuh"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -259,6 +261,9 @@ struct otgpu_ctx {
   DevBuf aff_rings, aff_slab, aff_slab2, aff_ops, cigar_off, cigars, cigar_len;  // gap-affine path
   DevBuf cigar_begin, cigars_packed;            // packed CIGAR output (device side)
   DevBuf bam_reads, bam_cigar, bam_seq4, bam_status, bam_coords, bam_plan;  // read extraction
+  DevBuf ppoa_in, ppoa_ws, ppoa_out;              // partial-order consensus: inputs, graph pools, strings
+  std::vector<char> h_ppoa;                       // packed consensus strings of the last call
+  std::vector<uint64_t> h_ppoa_begin;
   DevBuf bam_out, bam_begin, bam_len, gather_index;  // extracted reads, kept on the device
   uint32_t extracted_reads = 0;              // records of the last otgpu_extract_reads call (0: none)
   std::vector<uint32_t> extracted_len;       // their lengths (host copy)
@@ -485,6 +490,7 @@ void otgpu_destroy(otgpu_ctx* ctx) {
                     &ctx->cigar_len, &ctx->cigar_begin, &ctx->cigars_packed, &ctx->bam_reads,
                     &ctx->bam_cigar, &ctx->bam_seq4, &ctx->bam_status, &ctx->bam_coords, &ctx->bam_plan,
                     &ctx->bam_out, &ctx->bam_begin, &ctx->bam_len, &ctx->gather_index,
+                    &ctx->ppoa_in, &ctx->ppoa_ws, &ctx->ppoa_out,
                     &ctx->kde_values, &ctx->kde_off, &ctx->kde_grid, &ctx->kde_h, &ctx->kde_inv_h,
                     &ctx->kde_out};
   for (DevBuf* b : bufs)
@@ -1408,6 +1414,145 @@ extern "C" int otgpu_kde_densities(otgpu_ctx* ctx, const double* values, const u
   CK(cudaGetLastError());
   CK(cudaMemcpyAsync(densities_out, ctx->kde_out.p, (size_t)n_regions * n_grid * 8, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
+  return OTGPU_OK;
+}
+
+// ---- partial-order consensus (ppoa.cuh) ----------------------------------------------------------
+extern "C" int otgpu_ppoa_consensus(otgpu_ctx* ctx, const uint8_t* bases, uint64_t n_bases,
+                                    const uint64_t* read_off, const uint32_t* read_len, uint32_t n_reads,
+                                    const otgpu_ppoa_graph* graphs, uint32_t n_graphs,
+                                    const otgpu_ppoa_member* members, uint32_t n_members,
+                                    const char* cigars, uint64_t n_cigar_bytes, int32_t* consensus_len,
+                                    const char** consensus, const uint64_t** begin) {
+  if (!ctx || !consensus || !begin) return OTGPU_ERR_ARGS;
+  *consensus = nullptr;
+  *begin = nullptr;
+  if ((!bases && n_bases) || ((!read_off || !read_len) && n_reads) || (!graphs && n_graphs) ||
+      (!members && n_members) || (!cigars && n_cigar_bytes) || (!consensus_len && n_graphs))
+    return OTGPU_ERR_ARGS;
+  for (uint32_t r = 0; r < n_reads; ++r)
+    if (read_off[r] + read_len[r] > n_bases) return OTGPU_ERR_ARGS;
+  std::vector<PpoaGraphDev> gd;
+  std::vector<uint32_t> nonm;
+  try {
+    gd.resize(n_graphs);
+    nonm.resize(n_members);
+    ctx->h_ppoa_begin.assign((size_t)n_graphs + 1, 0);
+  } catch (...) {
+    return OTGPU_ERR_OOM;
+  }
+  for (uint32_t m = 0; m < n_members; ++m) {
+    const otgpu_ppoa_member& M = members[m];
+    if (M.read >= n_reads || M.cigar_off > n_cigar_bytes || M.cigar_len > n_cigar_bytes - M.cigar_off)
+      return OTGPU_ERR_ARGS;
+    uint32_t k = 0;
+    const char* c = cigars + M.cigar_off;
+    for (uint32_t i = 0; i < M.cigar_len; ++i) k += c[i] != 'M';
+    nonm[m] = k;
+  }
+  // pool sizes: a graph gains at most one node per X / I and at most two edges per non-M operation
+  uint64_t nodes = 0, edges = 0, starts = 0;
+  for (uint32_t g = 0; g < n_graphs; ++g) {
+    const otgpu_ppoa_graph& G = graphs[g];
+    if (G.backbone >= n_reads || G.first_member > n_members || G.n_members > n_members - G.first_member)
+      return OTGPU_ERR_ARGS;
+    uint64_t k = 0;
+    for (uint32_t m = 0; m < G.n_members; ++m) k += nonm[G.first_member + m];
+    const uint64_t nb = read_len[G.backbone];
+    const uint64_t ncap = nb + k + 1, ecap = nb + 2 * k + 2;
+    if (ncap >= 0x7fffffffull || ecap >= 0x7fffffffull) return OTGPU_ERR_ARGS;
+    PpoaGraphDev& D = gd[g];
+    D.backbone = G.backbone; D.first_member = G.first_member; D.n_members = G.n_members;
+    D.c = G.c; D.t = G.t;
+    D.node_off = nodes; D.edge_off = edges; D.start_off = starts;
+    D.node_cap = (uint32_t)ncap; D.edge_cap = (uint32_t)ecap;
+    nodes += ncap; edges += ecap; starts += (uint64_t)G.n_members + 2;
+  }
+  if (n_graphs == 0) {
+    *begin = ctx->h_ppoa_begin.data();
+    return OTGPU_OK;
+  }
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  CK(cudaStreamSynchronize(st));
+  auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+  // inputs in one buffer
+  const size_t i_bases = 0, i_off = i_bases + al(n_bases + 16), i_len = i_off + al((size_t)n_reads * 8 + 8),
+               i_graphs = i_len + al((size_t)n_reads * 4 + 4), i_members = i_graphs + al(gd.size() * sizeof(PpoaGraphDev)),
+               i_cigars = i_members + al((size_t)n_members * sizeof(PpoaMemberDev) + 16),
+               i_cursor = i_cigars + al(n_cigar_bytes + 16), i_lens = i_cursor + 256,
+               i_end = i_lens + al((size_t)n_graphs * 4);
+  static_assert(sizeof(PpoaMemberDev) == sizeof(otgpu_ppoa_member), "member layout");
+  RS(ppoa_in, i_end);
+  uint8_t* I = static_cast<uint8_t*>(ctx->ppoa_in.p);
+  // pools in one buffer
+  PpoaPools P;
+  size_t w = 0;
+  uint8_t* W = nullptr;
+  auto carve = [&](size_t bytes) { const size_t at = w; w += al(bytes); return at; };
+  const size_t o_base = carve(nodes), o_ending = carve(nodes), o_done = carve(nodes), o_head = carve(nodes * 4),
+               o_tail = carve(nodes * 4), o_inoff = carve((nodes + n_graphs + 1) * 4), o_fill = carve(nodes * 4),
+               o_pending = carve(nodes * 4), o_weight = carve(nodes * 4), o_pred = carve(nodes * 4),
+               o_queue = carve(nodes * 4), o_esink = carve(edges * 4), o_ew = carve(edges * 4),
+               o_enext = carve(edges * 4), o_insrc = carve(edges * 4), o_inpos = carve(edges * 4),
+               o_inw = carve(edges * 4), o_starts = carve(starts * 4);
+  RS(ppoa_ws, w + 256);
+  RS(ppoa_out, nodes + 16);
+  W = static_cast<uint8_t*>(ctx->ppoa_ws.p);
+  P.base = W + o_base; P.ending = W + o_ending; P.done = W + o_done;
+  P.head = reinterpret_cast<int32_t*>(W + o_head); P.tail = reinterpret_cast<int32_t*>(W + o_tail);
+  P.in_off = reinterpret_cast<uint32_t*>(W + o_inoff); P.fill = reinterpret_cast<uint32_t*>(W + o_fill);
+  P.pending = reinterpret_cast<uint32_t*>(W + o_pending); P.weight = reinterpret_cast<float*>(W + o_weight);
+  P.pred = reinterpret_cast<int32_t*>(W + o_pred); P.queue = reinterpret_cast<uint32_t*>(W + o_queue);
+  P.e_sink = reinterpret_cast<uint32_t*>(W + o_esink); P.e_w = reinterpret_cast<float*>(W + o_ew);
+  P.e_next = reinterpret_cast<int32_t*>(W + o_enext); P.in_src = reinterpret_cast<uint32_t*>(W + o_insrc);
+  P.in_pos = reinterpret_cast<uint32_t*>(W + o_inpos); P.in_w = reinterpret_cast<float*>(W + o_inw);
+  P.starts = reinterpret_cast<uint32_t*>(W + o_starts);
+  if (n_bases) CK(cudaMemcpyAsync(I + i_bases, bases, n_bases, cudaMemcpyHostToDevice, st));
+  if (n_reads) {
+    CK(cudaMemcpyAsync(I + i_off, read_off, (size_t)n_reads * 8, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(I + i_len, read_len, (size_t)n_reads * 4, cudaMemcpyHostToDevice, st));
+  }
+  CK(cudaMemcpyAsync(I + i_graphs, gd.data(), gd.size() * sizeof(PpoaGraphDev), cudaMemcpyHostToDevice, st));
+  if (n_members)
+    CK(cudaMemcpyAsync(I + i_members, members, (size_t)n_members * sizeof(PpoaMemberDev), cudaMemcpyHostToDevice, st));
+  if (n_cigar_bytes) CK(cudaMemcpyAsync(I + i_cigars, cigars, n_cigar_bytes, cudaMemcpyHostToDevice, st));
+  CK(cudaMemsetAsync(I + i_cursor, 0, 256, st));
+  const int ctas = (int)std::min<uint64_t>(((uint64_t)n_graphs + 3) / 4, (uint64_t)ctx->n_sm * 8);
+  k_ppoa<<<ctas, 128, 0, st>>>(reinterpret_cast<const PpoaGraphDev*>(I + i_graphs), n_graphs,
+                               reinterpret_cast<const PpoaMemberDev*>(I + i_members), I + i_bases,
+                               reinterpret_cast<const uint64_t*>(I + i_off),
+                               reinterpret_cast<const uint32_t*>(I + i_len),
+                               reinterpret_cast<const char*>(I + i_cigars), P,
+                               reinterpret_cast<unsigned int*>(I + i_cursor),
+                               static_cast<char*>(ctx->ppoa_out.p), reinterpret_cast<int32_t*>(I + i_lens));
+  ctx->stats.kernel_launches++;
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(consensus_len, I + i_lens, (size_t)n_graphs * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  uint64_t total = 0;
+  for (uint32_t g = 0; g < n_graphs; ++g) {
+    if (consensus_len[g] < 0) {
+      snprintf(ctx->err, sizeof(ctx->err), "partial-order graph %u outgrew its pools", g);
+      return OTGPU_ERR_STATE;
+    }
+    ctx->h_ppoa_begin[g] = total;
+    total += (uint64_t)consensus_len[g];
+  }
+  ctx->h_ppoa_begin[n_graphs] = total;
+  try {
+    ctx->h_ppoa.resize(total + 1);
+  } catch (...) {
+    return OTGPU_ERR_OOM;
+  }
+  for (uint32_t g = 0; g < n_graphs; ++g)  // only the strings leave the device
+    if (consensus_len[g] > 0)
+      CK(cudaMemcpyAsync(ctx->h_ppoa.data() + ctx->h_ppoa_begin[g],
+                         static_cast<const char*>(ctx->ppoa_out.p) + gd[g].node_off, (size_t)consensus_len[g],
+                         cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  *consensus = ctx->h_ppoa.data();
+  *begin = ctx->h_ppoa_begin.data();
   return OTGPU_OK;
 }
 
