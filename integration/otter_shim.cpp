@@ -593,6 +593,7 @@ double ref_assemble_regions(const char* bases, const uint64_t* off, const uint32
   std::vector<std::vector<double>> dens(n_regions);
   std::vector<double> bandw(n_regions, 0.01);
   const bool host_kde = getenv("OTREF_HOST_KDE") != nullptr;  // A/B: the reference's own otter_hclust
+  const bool device_ppoa = getenv("OTREF_DEVICE_PPOA") != nullptr;  // A/B: the graphs on the GPU too
   // the second device stage is issued from its own thread (wave_b200.hpp): its own edit aligner,
   // kept for the life of the process like the thread's other aligners (a context is not free)
   static wfa::WFAlignerEdit edit2(wfa::WFAligner::Score, wfa::WFAligner::MemoryMed);
@@ -660,11 +661,21 @@ double ref_assemble_regions(const char* bases, const uint64_t* off, const uint32
       rapid_consensus_alignments(A.affine, batch);
       for (size_t i = 0; i < batch.size(); ++i) cjobs[owner[i]] = std::move(batch[i]);
     });
+    if (device_ppoa) timed("partial-order consensus (GPU)", [&] {
+      std::vector<ConsensusJob*> jp;
+      std::vector<std::vector<ANALLELE>*> ap;
+      for (uint32_t g = a; g < b; ++g)
+        if (!W[g].valid.empty()) {
+          jp.push_back(&cjobs[g]);
+          ap.push_back(&W[g].alleles);
+        }
+      rapid_consensus_finish_device(ignore_haps, A.affine, jp, ap);
+    });
   };
   st.host2 = [&](uint32_t a, uint32_t b) {
     timed("partial-order consensus (host)", [&] {
       blocks(a, b, [&](uint32_t g) {
-        if (!W[g].valid.empty()) rapid_consensus_finish(ignore_haps, cjobs[g], W[g].alleles);
+        if (!W[g].valid.empty() && !device_ppoa) rapid_consensus_finish(ignore_haps, cjobs[g], W[g].alleles);
         publish(g);
       });
     });

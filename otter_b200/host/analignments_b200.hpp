@@ -127,6 +127,12 @@ void rapid_consensus(const bool& ignore_haps, std::vector<ANREAD>& reads, std::v
 void rapid_consensus_finish(const bool& ignore_haps, ConsensusJob& job,
                             std::vector<ANALLELE>& alleles);
 
+// The same host half for many jobs at once, with the partial-order consensus of every allele of
+// the batch in ONE device call (otgpu_ppoa_consensus): alleles[j] receives job j's alleles.
+void rapid_consensus_finish_device(const bool& ignore_haps, wfa::WFAligner& aligner2,
+                                   std::vector<ConsensusJob*>& jobs,
+                                   std::vector<std::vector<ANALLELE>*>& alleles);
+
 #ifdef OTTER_B200_IN_TREE
 #include "anfahelper.hpp"
 // Reference signature; the alignment calls inside run batched on the GPU.

@@ -324,47 +324,65 @@ void rapid_consensus(const bool& ignore_haps, std::vector<ANREAD>& reads, std::v
   rapid_consensus_finish(ignore_haps, one[0], alleles);
 }
 
+namespace {
+// Everything rapid_consensus does for one allele except the graph (src/analignments.cpp:227-258):
+// coverages, standard error, haplotag check.  Returns true when the allele needs the partial-order
+// consensus (three reads or more); otherwise allele.seq is already final.
+bool allele_bookkeeping(const bool& ignore_haps, ConsensusJob& job, int label, ANALLELE& allele) {
+  std::vector<ANREAD>& reads = *job.reads;
+  DistMatrix& valid_distmatrix = *job.valid_distmatrix;
+  const ConsensusPlan& P = job.plans[label];
+  allele.tcov = reads.size();               // :227-229
+  allele.acov = P.members.size() + 1;
+  allele.scov = P.valid_reads.size();
+  if (P.valid_pos.size() == 1) allele.se = 0;  // :231-237
+  else if (P.valid_pos.size() == 2) allele.se = valid_distmatrix.get_dist(P.valid_pos[0], P.valid_pos[1]);
+  else {
+    std::vector<double> d;
+    for (const auto& i : P.valid_pos)
+      if ((int)i != P.rep_pos) d.emplace_back(valid_distmatrix.get_dist(i, P.rep_pos));
+    allele.se = standard_error(d);
+  }
+  if (!ignore_haps) {  // :239-256
+    int ps = -1, hp = -1;
+    bool conflicting = false;
+    for (const auto& i : P.valid_reads) {
+      if (ps < 0) ps = reads[i].hpt.ps;
+      else if (ps != reads[i].hpt.ps) conflicting = true;
+      if (hp < 0) hp = reads[i].hpt.hp;
+      else if (hp != reads[i].hpt.hp) conflicting = true;
+    }
+    if (conflicting) {
+      std::cerr << "ERROR: conflicting haplotag information:\n";
+      for (const auto& i : P.valid_reads)
+        std::cerr << reads[i].name << '\t' << reads[i].hpt.ps << '\t' << reads[i].hpt.hp << '\n';
+      std::cerr << std::endl;
+      exit(1);
+    }
+    allele.hpt = reads[P.rep].hpt;
+  }
+  if (P.members.size() + 1 <= 2) {  // :258
+    allele.seq = reads[P.valid_reads.front()].seq;
+    return false;
+  }
+  return true;
+}
+// adjust_weights parameters of an allele with n reads (:285-288)
+void damping(size_t n_reads_of_allele, float& c, float& t) {
+  c = n_reads_of_allele * 0.4;
+  t = 0.3;
+  if (n_reads_of_allele < 4) c = 1.0;
+}
+}  // namespace
+
 void rapid_consensus_finish(const bool& ignore_haps, ConsensusJob& job,
                             std::vector<ANALLELE>& alleles) {
   std::vector<ANREAD>& reads = *job.reads;
-  DistMatrix& valid_distmatrix = *job.valid_distmatrix;
   const int total_alleles = job.total_alleles;
   for (int label = 0; label < total_alleles; ++label) {
     const ConsensusPlan& P = job.plans[label];
     auto& allele = alleles[label];
-    allele.tcov = reads.size();               // :227-229
-    allele.acov = P.members.size() + 1;
-    allele.scov = P.valid_reads.size();
-    if (P.valid_pos.size() == 1) allele.se = 0;  // :231-237
-    else if (P.valid_pos.size() == 2) allele.se = valid_distmatrix.get_dist(P.valid_pos[0], P.valid_pos[1]);
-    else {
-      std::vector<double> d;
-      for (const auto& i : P.valid_pos)
-        if ((int)i != P.rep_pos) d.emplace_back(valid_distmatrix.get_dist(i, P.rep_pos));
-      allele.se = standard_error(d);
-    }
-    if (!ignore_haps) {  // :239-256
-      int ps = -1, hp = -1;
-      bool conflicting = false;
-      for (const auto& i : P.valid_reads) {
-        if (ps < 0) ps = reads[i].hpt.ps;
-        else if (ps != reads[i].hpt.ps) conflicting = true;
-        if (hp < 0) hp = reads[i].hpt.hp;
-        else if (hp != reads[i].hpt.hp) conflicting = true;
-      }
-      if (conflicting) {
-        std::cerr << "ERROR: conflicting haplotag information:\n";
-        for (const auto& i : P.valid_reads)
-          std::cerr << reads[i].name << '\t' << reads[i].hpt.ps << '\t' << reads[i].hpt.hp << '\n';
-        std::cerr << std::endl;
-        exit(1);
-      }
-      allele.hpt = reads[P.rep].hpt;
-    }
-    if (P.members.size() + 1 <= 2) {  // :258
-      allele.seq = reads[P.valid_reads.front()].seq;
-      continue;
-    }
+    if (!allele_bookkeeping(ignore_haps, job, label, allele)) continue;
     otb200::Ppoa poa;  // src/anppoa.hpp restated (ppoa_b200.hpp)
     poa.init(reads[P.rep].seq);
     for (size_t m = 0; m < P.members.size(); ++m) {
@@ -372,11 +390,80 @@ void rapid_consensus_finish(const bool& ignore_haps, ConsensusJob& job,
       std::string cigar = P.cigars[m];
       poa.insert_alignment(read.seq, cigar, read.is_spanning_l, read.is_spanning_r);  // :282
     }
-    float c = (P.members.size() + 1) * 0.4;  // :285-288
-    float t = 0.3;
-    if (P.members.size() + 1 < 4) c = 1.0;
+    float c, t;
+    damping(P.members.size() + 1, c, t);
     poa.adjust_weights(c, t);
     poa.consensus(allele.seq);
+    if (allele.seq.empty()) allele.seq = "N";
+  }
+}
+
+// The same for many jobs, with the partial-order consensus of every allele in ONE device call
+// (otgpu_ppoa_consensus, csrc/ppoa.cuh): the host keeps the bookkeeping, the graphs are built and
+// walked on the GPU.  Same alleles as rapid_consensus_finish job by job.
+void rapid_consensus_finish_device(const bool& ignore_haps, wfa::WFAligner& aligner2,
+                                   std::vector<ConsensusJob*>& jobs,
+                                   std::vector<std::vector<ANALLELE>*>& alleles) {
+  otgpu_ctx* ctx = aligner2.context();
+  if (!ctx) die("rapid_consensus", OTGPU_ERR_NO_DEVICE, nullptr);
+  struct Slot { size_t job; int label; };
+  std::vector<Slot> slots;
+  std::vector<otgpu_ppoa_graph> graphs;
+  std::vector<otgpu_ppoa_member> members;
+  std::vector<uint64_t> off;
+  std::vector<uint32_t> len;
+  std::string bases, cigars;
+  for (size_t j = 0; j < jobs.size(); ++j) {
+    ConsensusJob& job = *jobs[j];
+    std::vector<ANREAD>& reads = *job.reads;
+    size_t first_read = (size_t)-1;  // this job's reads enter the batch once, on first use
+    for (int label = 0; label < job.total_alleles; ++label) {
+      if (!allele_bookkeeping(ignore_haps, job, label, (*alleles[j])[label])) continue;
+      if (first_read == (size_t)-1) {
+        first_read = off.size();
+        for (const ANREAD& r : reads) {
+          off.push_back(bases.size());
+          len.push_back((uint32_t)r.seq.size());
+          bases += r.seq;
+        }
+      }
+      const ConsensusPlan& P = job.plans[label];
+      otgpu_ppoa_graph g;
+      g.backbone = (uint32_t)(first_read + P.rep);
+      g.first_member = (uint32_t)members.size();
+      g.n_members = (uint32_t)P.members.size();
+      damping(P.members.size() + 1, g.c, g.t);
+      for (size_t m = 0; m < P.members.size(); ++m) {
+        const ANREAD& read = reads[P.members[m]];
+        otgpu_ppoa_member M;
+        M.read = (uint32_t)(first_read + P.members[m]);
+        M.flags = (read.is_spanning_l ? 1u : 0u) | (read.is_spanning_r ? 2u : 0u);
+        M.cigar_off = cigars.size();
+        M.cigar_len = (uint32_t)P.cigars[m].size();
+        M.reserved = 0;
+        cigars += P.cigars[m];
+        members.push_back(M);
+      }
+      graphs.push_back(g);
+      slots.push_back({j, label});
+    }
+  }
+  if (graphs.empty()) return;
+  std::vector<int32_t> clen(graphs.size());
+  const char* cons = nullptr;
+  const uint64_t* begin = nullptr;
+  int st;
+  {
+    std::lock_guard<otb200::DeviceTurn> turn(otb200::device_turn(aligner2.device()));
+    st = otgpu_ppoa_consensus(ctx, reinterpret_cast<const uint8_t*>(bases.data()), bases.size(), off.data(),
+                              len.data(), (uint32_t)off.size(), graphs.data(), (uint32_t)graphs.size(),
+                              members.data(), (uint32_t)members.size(), cigars.data(), cigars.size(),
+                              clen.data(), &cons, &begin);
+  }
+  if (st != OTGPU_OK) die("partial-order consensus", st, ctx);
+  for (size_t i = 0; i < slots.size(); ++i) {
+    ANALLELE& allele = (*alleles[slots[i].job])[slots[i].label];
+    allele.seq.assign(cons + begin[i], (size_t)clen[i]);
     if (allele.seq.empty()) allele.seq = "N";
   }
 }
