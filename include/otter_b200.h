@@ -151,6 +151,14 @@ int otgpu_region_edit_scores_hooked(otgpu_ctx* ctx, const uint8_t* bases, uint64
  * chunk overlaps the alignment of the previous one and device memory stays bounded; scores are
  * identical to a single batch.  Number of chunks the last otgpu_region_edit_scores call used: */
 uint64_t otgpu_last_chunk_count(const otgpu_ctx* ctx);
+/* The score kernel for reads up to 8 kb comes in two flavours that differ only in speed: 64-bit
+ * first comparison windows (noisy reads), or 32-bit first windows with 128-bit continuations
+ * (low-error reads, about 5 % faster on HiFi-shaped batches, slower on noisy ones).  Each call
+ * counts its low-error pairs (>= 32 bases per score step) and the NEXT call on the context takes
+ * the second flavour when they were at least 30 %; a fresh context starts with the first.
+ * Returns the flavour the next call will use (0 or 1).  No counterpart in the reference: both
+ * flavours compute the reference's scores. */
+int otgpu_first_window(const otgpu_ctx* ctx);
 
 
 /* ---- split-phase calls (inputs stay resident in HBM between phases) ---------------------- */

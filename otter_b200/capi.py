@@ -14,7 +14,7 @@ SYMBOLS = [
     "otgpu_host_free", "otgpu_edit_scores", "otgpu_region_edit_scores",
     "otgpu_batch_upload_regions", "otgpu_batch_upload_pairs", "otgpu_batch_align",
     "otgpu_batch_download", "otgpu_synchronize", "otgpu_last_align_ms", "otgpu_affine_cigars",
-    "otgpu_edit_cigars", "otgpu_last_chunk_count", "otgpu_affine_cigars_packed",
+    "otgpu_edit_cigars", "otgpu_last_chunk_count", "otgpu_first_window", "otgpu_affine_cigars_packed",
     "otgpu_edit_cigars_packed", "otgpu_extract_reads", "otgpu_kde_densities",
     "otgpu_region_edit_scores_hooked", "otgpu_region_edit_scores_extracted",
     "otgpu_edit_scores_static", "otgpu_ppoa_consensus",
@@ -108,6 +108,8 @@ def lib():
         l.otgpu_kde_densities.argtypes = [vp, vp, vp, u32, vp, vp, u32, vp]
         l.otgpu_last_chunk_count.restype = u64
         l.otgpu_last_chunk_count.argtypes = [vp]
+        l.otgpu_first_window.restype = C.c_int
+        l.otgpu_first_window.argtypes = [vp]
         _lib = l
     return _lib
 
@@ -215,6 +217,10 @@ class Context:
 
     def last_chunk_count(self):
         return int(self._l.otgpu_last_chunk_count(self._h))
+
+    def first_window(self):
+        """Flavour of the <= 8 kb score kernel the next call will use (otgpu_first_window)."""
+        return int(self._l.otgpu_first_window(self._h))
 
     def edit_cigars(self, bases, off, lens, pairs):
         """Edit distance with CIGAR (compare's aligner) -> (scores, CIGAR bytes | status)."""

@@ -177,7 +177,10 @@ __device__ __noinline__ int wfa_edit_pair_hbm(int32_t* ws, int mask, const EditJ
 // CAP = 1024 keeps 4 CTAs (32 warps) per SM; 2048 (3 CTAs) is for batches of long reads, whose
 // wavefronts pass a thousand diagonals.
 constexpr size_t ring_bytes(int cap) { return (size_t)(kWarpsPerCta + 1) * cap * 4; }
-template <int CAP>
+// FW: first window of an extension (wfa_edit.cuh, first_window): 0 = 64 bits, 1 = 32 bits and
+// 128-bit continuations, for batches of low-error reads.  Scores are the same; the host picks per
+// launch from what the previous batch on the context looked like (ctr->v[5], below).
+template <int CAP, int FW = 0>
 __global__ void __launch_bounds__(kCtaThreads, CAP == 2048 ? 3 : OTGPU_ALIGN_MIN_CTAS)
 k_align(DevBatch b, Counters* __restrict__ ctr, const uint32_t* __restrict__ list, int count_slot,
         int cursor_slot, uint32_t* __restrict__ ovf_list, int32_t* __restrict__ wide_ws,
@@ -196,6 +199,7 @@ k_align(DevBatch b, Counters* __restrict__ ctr, const uint32_t* __restrict__ lis
     ring.base = a0 + warp * (CAP * 4);
   }
   const unsigned long long limit = WIDE ? ctr->v[1] : (count_slot < 0 ? b.n_pairs : ctr->v[count_slot]);
+  unsigned fast = 0;  // pairs of this warp that advanced >= kFwRun bases per score step
   for (;;) {
     unsigned long long q = 0;
     if (lane == 0) q = atomicAdd(&ctr->v[WIDE ? 2 : cursor_slot], 1ull);
@@ -217,14 +221,15 @@ k_align(DevBatch b, Counters* __restrict__ ctr, const uint32_t* __restrict__ lis
     if (bytes) {
       J.words = reinterpret_cast<const uint32_t*>(b.bases);
       J.P = view8(b, pr.pattern); J.T = view8(b, pr.text);
-      score = wfa_edit_pair<8, CAP>(ring, J, lane);
+      score = wfa_edit_pair<8, CAP, FW>(ring, J, lane);
       if (!WIDE && lane == 0) atomicAdd(&ctr->v[3], 1ull);
     } else {
       J.words = b.packed;
       J.P = view2(b, pr.pattern); J.T = view2(b, pr.text);
-      score = wfa_edit_pair<2, CAP>(ring, J, lane);
+      score = wfa_edit_pair<2, CAP, FW>(ring, J, lane);
     }
     __syncwarp();
+    if (CAP == 1024 && score >= 0 && max(J.plen, J.tlen) >= kFwRun * score) ++fast;
     if (CAP == 2048 && score == kScoreOverflow && wide_ws != nullptr) {
       int32_t* ws = wide_ws + (size_t)(blockIdx.x * kWarpsPerCta + warp) * wide_cap;
       score = bytes ? wfa_edit_pair_hbm<8>(ws, wide_cap - 1, J, lane)
@@ -241,6 +246,7 @@ k_align(DevBatch b, Counters* __restrict__ ctr, const uint32_t* __restrict__ lis
       }
     }
   }
+  if (CAP == 1024 && lane == 0 && fast) atomicAdd(&ctr->v[5], (unsigned long long)fast);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -285,6 +291,12 @@ struct otgpu_ctx {
   uint32_t n_reads = 0, n_regions = 0, max_len = 0;
   int grid_main = 0, grid_main_long = 0, grid_wide = 0, wide_cap = 0, wide_per_sm = 2;
   int force_ring = 0;  // OTGPU_RING_SLOTS=1024|2048 at otgpu_create: pin the ring tier (tests)
+  // First window of the 1,024-slot kernel (k_align<1024, FW>): the short one when at least 30 % of
+  // the previous batch on this context were low-error pairs (>= kFwRun bases per score step: reads
+  // of the same allele at <= 1.5 % error each; noisy reads reach 10-16).  Only speed depends on it.
+  // OTGPU_FIRST_WINDOW=0|1 at otgpu_create pins it (tests, A/B).
+  int fw_force = -1;
+  bool fw_next = false, fw_counted = false;
   bool wide_two_pass = false;  // OTGPU_WIDE_TWO_PASS=1 at otgpu_create: always use k_align<0> (tests)
   // streaming of large region batches (otgpu_region_edit_scores): a second context on the same
   // device, made on first use, so that chunk i+1 uploads while chunk i aligns
@@ -460,6 +472,9 @@ int otgpu_create(int device, otgpu_ctx** out) {
     const int v = atoi(rs);
     if (v == 1024 || v == 2048) ctx->force_ring = v;
   }
+  if (const char* fw = getenv("OTGPU_FIRST_WINDOW")) {
+    if (fw[0] == '0' || fw[0] == '1') ctx->fw_force = fw[0] - '0';
+  }
   if (const char* tp = getenv("OTGPU_WIDE_TWO_PASS")) ctx->wide_two_pass = atoi(tp) != 0;
   if (const char* cm = getenv("OTGPU_CHUNK_MB")) {
     const long v = atol(cm);
@@ -511,6 +526,9 @@ const char* otgpu_last_cuda_error(const otgpu_ctx* ctx) { return ctx ? ctx->err 
 void* otgpu_stream(otgpu_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
 
 uint64_t otgpu_last_chunk_count(const otgpu_ctx* ctx) { return ctx ? ctx->n_chunks_last : 0; }
+int otgpu_first_window(const otgpu_ctx* ctx) {
+  return ctx ? (ctx->fw_force >= 0 ? ctx->fw_force : (ctx->fw_next ? 1 : 0)) : 0;
+}
 
 int otgpu_get_stats(const otgpu_ctx* ctx, otgpu_stats* out) {
   if (!ctx || !out) return OTGPU_ERR_ARGS;
@@ -684,8 +702,11 @@ int otgpu_batch_align(otgpu_ctx* ctx) {
     // one HBM ring per warp of this launch (the wide workspace holds grid_wide CTAs' worth): pairs
     // that outgrow the shared ring continue inside the kernel; else they wait for k_align<0>
     int32_t* ws = grid <= ctx->grid_wide && !ctx->wide_two_pass ? static_cast<int32_t*>(ctx->wide_ws.p) : nullptr;
+    ctx->fw_counted = !long_ring;
     if (long_ring)
       k_align<2048><<<grid, kCtaThreads, ring_bytes(2048), st>>>(b, ctr, order, -1, 0, ovf, ws, ctx->wide_cap);
+    else if (ctx->fw_force >= 0 ? ctx->fw_force == 1 : ctx->fw_next)
+      k_align<1024, 1><<<grid, kCtaThreads, ring_bytes(1024), st>>>(b, ctr, order, -1, 0, ovf, ws, ctx->wide_cap);
     else
       k_align<1024><<<grid, kCtaThreads, ring_bytes(1024), st>>>(b, ctr, order, -1, 0, ovf, ws, ctx->wide_cap);
     CK(cudaEventRecord(ctx->ev[3], st));
@@ -729,6 +750,7 @@ int otgpu_batch_download(otgpu_ctx* ctx, int32_t* scores_out, uint64_t n_scores)
   ctx->stats.n_pairs = ctx->n_pairs;
   ctx->stats.n_pairs_wide = hc->v[1] + hc->v[4];
   ctx->stats.n_pairs_8bit = hc->v[3];
+  if (ctx->fw_counted && ctx->n_pairs) ctx->fw_next = hc->v[5] * 10 >= (unsigned long long)ctx->n_pairs * 3;
   return OTGPU_OK;
 }
 

@@ -43,6 +43,7 @@ constexpr int kMinWfLen = 10;   // wavefront_attributes.c:74
 constexpr int kMaxDist = 50;    // wavefront_attributes.c:75
 constexpr int kPruneLen = 1000; // wavefront_compute_edit.c:224
 constexpr int kScoreOverflow = -2;  // internal: live width exceeded the shared-memory ring
+constexpr int kFwRun = 32;  // a pair advancing >= this many bases per score step is a low-error pair (k_align's count)
 constexpr int kBigDist = 1 << 30;   // distance of a null offset, wavefront_heuristic.c:118
 
 // ---- wavefront ring ---------------------------------------------------------------------------
@@ -317,6 +318,29 @@ __device__ __forceinline__ uint32_t first_diff(const EditJob& J, int v, int h) {
   return bit >> Pack<BITS>::kLogBits;
 }
 
+// The same over one 32-bit window (two words per read: kWin/2 - 1 compared bases).
+template <int BITS>
+__device__ __forceinline__ uint32_t first_diff_half(const EditJob& J, int v, int h) {
+  const int a = (BITS == 2) ? v : J.P.sh0 + v, b = (BITS == 2) ? h : J.T.sh0 + h;
+  const uint32_t* p = J.words + (J.P.word0 + (uint32_t)(a >> Pack<BITS>::kLogBpw));
+  const uint32_t* t = J.words + (J.T.word0 + (uint32_t)(b >> Pack<BITS>::kLogBpw));
+  const uint32_t pw = __funnelshift_r(__ldg(p), __ldg(p + 1), a << Pack<BITS>::kLogBits);
+  const uint32_t tw = __funnelshift_r(__ldg(t), __ldg(t + 1), b << Pack<BITS>::kLogBits);
+  return (uint32_t)(__ffs((pw ^ tw) | 0x80000000u) - 1) >> Pack<BITS>::kLogBits;
+}
+// First window of an extension.  FW = 0: 64 bits (31 compared bases at 2 bit), what noisy reads
+// want - most of their runs end inside it.  FW = 1: 32 bits (15 bases: two loads and one funnel
+// shift less per read) followed by 128-bit continuation windows, for pairs whose runs are either
+// a few bases (off the alignment path) or hundreds (on it): low-error reads.  Same counts either
+// way.  The choice is made per launch (k_align<1024, FW>): a pair picking its own window inside
+// one kernel doubles the hot loop and ran 60 % slower (instruction cache), see profiles/README r3f.
+template <int BITS, int FW>
+__device__ __forceinline__ uint32_t first_window(const EditJob& J, int v, int h) {
+  return FW ? first_diff_half<BITS>(J, v, h) : first_diff<BITS>(J, v, h);
+}
+template <int BITS, int FW>
+struct FirstWin { static constexpr int kWE = FW ? Pack<BITS>::kWin / 2 - 1 : Pack<BITS>::kWin - 1; };
+
 // The same over a 128-bit window (four words per read: 63 compared bases at 2 bit, 15 at 8 bit, the
 // last base again a sentinel difference): continuation of a run that outlived its first window.
 // Touches up to four words past the word holding the position (buffers carry guards for that).
@@ -438,10 +462,11 @@ struct LaneConst {  // per-lane constants of the pass, made once per pair
         from_hi(opaque(g.first | ((g.gl + 1) & (G - 1)))) {}
 };
 
-template <int BITS, int CAP, bool EF, bool COMPUTE, bool EXTEND, int G>
+template <int BITS, int CAP, bool EF, bool COMPUTE, bool EXTEND, int G, int FW = 0>
 __device__ __forceinline__ void wf_pass(const Ring<CAP>& R, const EditJob& J, const Grp<G>& g,
                                         const LaneConst& C, WfState& S) {
-  constexpr int WE = Pack<BITS>::kWin - 1;
+  constexpr int WE = FirstWin<BITS, FW>::kWE;
+  constexpr bool WIDE_ALL = CAP != 1024 || FW != 0;
   const int plen = J.plen, tlen = J.tlen, ak = tlen - plen;
   const int clo = COMPUTE ? S.lo - 1 : S.lo, chi = COMPUTE ? S.hi + 1 : S.hi;
   const int mk0 = C.mk0, mk31 = C.mk31, from_lo = C.from_lo, from_hi = C.from_hi;
@@ -478,17 +503,17 @@ __device__ __forceinline__ void wf_pass(const Ring<CAP>& R, const EditJob& J, co
     const int rem0 = min(pr0, tr0), rem1 = min(pr1, tr1);
     const bool ok0 = (m0 | v0 | rem0) >= 0, ok1 = (m1 | v1 | rem1) >= 0;
     if (EXTEND) {
-      int n0 = (int)min(first_diff<BITS>(J, v0, m0), (uint32_t)rem0);
-      int n1 = (int)min(first_diff<BITS>(J, v1, m1), (uint32_t)rem1);
+      int n0 = (int)min(first_window<BITS, FW>(J, v0, m0), (uint32_t)rem0);
+      int n1 = (int)min(first_window<BITS, FW>(J, v1, m1), (uint32_t)rem1);
       // a count of WE = every compared base matched and more remain: rare, and tested on the
       // counts alone (lanes that are out of bounds may raise it spuriously; lcp_more re-checks)
       if (__any_sync(g.mask, (n0 == WE) | (n1 == WE))) {
         const bool c0 = ok0 && n0 == WE && rem0 > WE, c1 = ok1 && n1 == WE && rem1 > WE;
         if (__any_sync(g.mask, c0 | c1)) {  // each lane finishes one pending run per call
-          const int n = lcp_more<BITS, G, CAP != 1024>(J, g, c0 ? v0 : v1, c0 ? m0 : m1, c0 ? rem0 : rem1, c0 | c1,
-                                          c0 ? n0 : n1);
+          const int n = lcp_more<BITS, G, WIDE_ALL>(J, g, c0 ? v0 : v1, c0 ? m0 : m1, c0 ? rem0 : rem1, c0 | c1,
+                                                    c0 ? n0 : n1);
           if (c0) n0 = n; else n1 = n;
-          if (__any_sync(g.mask, c0 & c1)) n1 = lcp_more<BITS, G, CAP != 1024>(J, g, v1, m1, rem1, c0 & c1, n1);
+          if (__any_sync(g.mask, c0 & c1)) n1 = lcp_more<BITS, G, WIDE_ALL>(J, g, v1, m1, rem1, c0 & c1, n1);
         }
       }
       m0 += n0;
@@ -525,10 +550,10 @@ __device__ __forceinline__ void wf_pass(const Ring<CAP>& R, const EditJob& J, co
     const int v = m - k, pr = plen - v, tr = tlen - m, rem = min(pr, tr);
     const bool ok = (m | v | rem) >= 0;
     if (EXTEND) {
-      int n = (int)min(first_diff<BITS>(J, v, m), (uint32_t)rem);
+      int n = (int)min(first_window<BITS, FW>(J, v, m), (uint32_t)rem);
       if (__any_sync(g.mask, n == WE)) {
         const bool c = ok && n == WE && rem > WE;
-        if (__any_sync(g.mask, c)) n = lcp_more<BITS, G, CAP != 1024>(J, g, v, m, rem, c, n);
+        if (__any_sync(g.mask, c)) n = lcp_more<BITS, G, WIDE_ALL>(J, g, v, m, rem, c, n);
       }
       m += n;
       if (EF) fin |= ok && ((tr - n <= 0 && pr - n <= J.pe) || (pr - n <= 0 && tr - n <= J.te));
@@ -704,10 +729,11 @@ __device__ __forceinline__ int wf_edges(const Ring<CAP>& R, const int plen, cons
 // The ring is all nulls while the wavefront lives in registers; it is written back on the way out.
 // Same order of operations as wf_pass + wf_edges.  Returns 1 = alignment done, -1 = wavefront
 // empty, 0 = the next step needs more than 30 lanes (wavefront [S.lo,S.hi] is back in the ring).
-template <int BITS, int CAP, bool EF>
+template <int BITS, int CAP, bool EF, int FW = 0>
 __device__ __forceinline__ int wf_narrow_run(const Ring<CAP>& R, const EditJob& J, const int lane,
                                              WfState& S, int& s) {
-  constexpr int WE = Pack<BITS>::kWin - 1;
+  constexpr int WE = FirstWin<BITS, FW>::kWE;
+  constexpr bool WIDE_ALL = CAP != 1024 || FW != 0;
   const int plen = J.plen, tlen = J.tlen, ak = tlen - plen;
   const int dcap = max(plen, tlen);
   int lo = S.lo, hi = S.hi;
@@ -727,10 +753,10 @@ __device__ __forceinline__ int wf_narrow_run(const Ring<CAP>& R, const EditJob& 
     const int v = m - k, pr = plen - v, tr = tlen - m, rem = min(pr, tr);
     const bool ok = (m | v | rem) >= 0;
     // ---- extend (wavefront_extend.c:203-260) ----
-    int n = (int)min(first_diff<BITS>(J, v, m), (uint32_t)rem);
+    int n = (int)min(first_window<BITS, FW>(J, v, m), (uint32_t)rem);
     if (__any_sync(kFull, n == WE)) {
       const bool c = ok && n == WE && rem > WE;
-      if (__any_sync(kFull, c)) n = lcp_more<BITS, 32, CAP != 1024>(J, Grp<32>(lane), v, m, rem, c, n);
+      if (__any_sync(kFull, c)) n = lcp_more<BITS, 32, WIDE_ALL>(J, Grp<32>(lane), v, m, rem, c, n);
     }
     bool fin = false;
     if (EF) fin = ok && ((tr - n <= 0 && pr - n <= J.pe) || (pr - n <= 0 && tr - n <= J.te));
@@ -814,7 +840,7 @@ __device__ __forceinline__ bool wf_prune(const Ring<CAP>& R, const int plen, con
 
 // One pair on one warp.  Returns score >= 0, OTGPU_SCORE_UNFEASIBLE (-1), or kScoreOverflow
 // (-2, never when WIDE).
-template <int BITS, int CAP, bool EF>
+template <int BITS, int CAP, bool EF, int FW = 0>
 __device__ int wfa_edit_run(const Ring<CAP>& R, const EditJob& J, const int lane) {
   const int plen = J.plen, tlen = J.tlen, ak = tlen - plen;
   const int cap = R.cap();
@@ -843,7 +869,7 @@ __device__ int wfa_edit_run(const Ring<CAP>& R, const EditJob& J, const int lane
 
   while (st == 0) {
     if (S.hi - S.lo + 3 <= 30) {  // the computed range fits lanes 1..30: register-resident steps
-      st = wf_narrow_run<BITS, CAP, EF>(R, J, lane, S, s);
+      st = wf_narrow_run<BITS, CAP, EF, FW>(R, J, lane, S, s);
       continue;
     }
     ++s;
@@ -865,17 +891,17 @@ __device__ int wfa_edit_run(const Ring<CAP>& R, const EditJob& J, const int lane
       wf_pass<BITS, CAP, EF, false, true>(R, J, g, C, S);
       st = wf_edges<CAP, EF>(R, plen, tlen, g, S.lo, S.hi, S);
     } else {
-      wf_pass<BITS, CAP, EF, true, true>(R, J, g, C, S);
+      wf_pass<BITS, CAP, EF, true, true, 32, FW>(R, J, g, C, S);
       st = wf_edges<CAP, EF>(R, plen, tlen, g, S.lo - 1, S.hi + 1, S);
     }
   }
   return st > 0 ? s : -1;  // done | empty wavefront -> WF_STATUS_UNFEASIBLE
 }
 
-template <int BITS, int CAP>
+template <int BITS, int CAP, int FW = 0>
 __device__ __forceinline__ int wfa_edit_pair(const Ring<CAP>& R, const EditJob& J, const int lane) {
-  return J.pb >= 0 ? wfa_edit_run<BITS, CAP, true>(R, J, lane)
-                   : wfa_edit_run<BITS, CAP, false>(R, J, lane);
+  return J.pb >= 0 ? wfa_edit_run<BITS, CAP, true, FW>(R, J, lane)
+                   : wfa_edit_run<BITS, CAP, false, FW>(R, J, lane);
 }
 
 }  // namespace otgpu

@@ -394,6 +394,49 @@ def test_streamed_chunks_equal_single_batch(ctx):
         del os.environ["OTGPU_CHUNK_MB"]
 
 
+def test_first_window_follows_the_previous_batch_and_never_changes_scores(built, monkeypatch):
+    """k_align<1024> has two flavours (64-bit first windows / 32-bit first windows + 128-bit
+    continuations).  A context starts with the first, counts the low-error pairs of every call
+    and takes the second for the next call when they were >= 30 %.  Scores never depend on it."""
+    import otter_b200
+    rng = np.random.default_rng(77)
+    hifi = S.region_batch([S.tr_region(rng, 10, 1500, 0.005, extra_frac=0.2, n_rate=0.1) for _ in range(6)])
+    noisy = S.region_batch([S.tr_region(rng, 10, 1500, 0.06, extra_frac=0.2, n_rate=0.1) for _ in range(6)])
+    run = lambda c, B: c.region_edit_scores(B["bases"], B["off"], B["lens"], B["region_start"],
+                                            B["score_off"], B["n_scores"])
+    monkeypatch.delenv("OTGPU_FIRST_WINDOW", raising=False)
+    with otter_b200.Context(0) as c:
+        assert c.first_window() == 0
+        h0 = run(c, hifi)                     # 64-bit windows; counted as a low-error batch
+        assert c.first_window() == 1
+        h1 = run(c, hifi)                     # 32-bit windows
+        assert c.first_window() == 1
+        n1 = run(c, noisy)                    # still 32-bit windows (slower, same scores)
+        assert c.first_window() == 0
+        n0 = run(c, noisy)
+        assert c.first_window() == 0
+    assert np.array_equal(h0, h1) and np.array_equal(n0, n1)
+    for force in ("0", "1"):
+        monkeypatch.setenv("OTGPU_FIRST_WINDOW", force)
+        with otter_b200.Context(0) as c:
+            assert c.first_window() == int(force)
+            assert np.array_equal(run(c, hifi), h0) and np.array_equal(run(c, noisy), n0)
+            assert c.first_window() == int(force)
+    # and against the port, pair by pair
+    P = S.port()
+    for B, got in ((hifi, h0), (noisy, n0)):
+        rs, lens, off = B["region_start"], B["lens"], B["off"]
+        q = 0
+        for g in range(len(rs) - 1):
+            for i, j in itertools.combinations(range(int(rs[g]), int(rs[g + 1])), 2):
+                x = B["bases"][int(off[i]):int(off[i]) + int(lens[i])].tobytes()
+                y = B["bases"][int(off[j]):int(off[j]) + int(lens[j])].tobytes()
+                if len(x) < len(y):
+                    x, y = y, x
+                assert got[q] == P.wfo_edit_score(x, len(x), y, len(y), 0, 0, 0, 0, 0, None), (g, i, j)
+                q += 1
+
+
 def test_streamed_batch_with_trailing_empty_regions(built):
     """A streamed batch whose last regions hold no reads (region_start[g] == n_reads): they are
     folded into the last chunk instead of starting a chunk that would address read n_reads."""
