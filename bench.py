@@ -885,7 +885,9 @@ class Bench:
                     "d2h_bytes_per_step": int(B["n_scores"] * 4), "ms_per_step": e2e_ms / steps,
                     "gcups_equiv": tot_cells * steps / (e2e_ms * 1e-3) / 1e9},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k_align<2048>" if long_ring else "k_align<1024>",
+            "roofline": {"bound": "hbm",
+                         "kernel": "k_align<2048>" if long_ring else
+                                   ("k_align<1024, 1>" if ctx.first_window() else "k_align<1024, 0>"),
                          "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None,
                          "alg_bytes_per_launch": B["alg_bytes"], "kernel_ms": k_ms,
@@ -1165,6 +1167,15 @@ def main():
             Bc = workload_arrays(name, 0, nreg)
             r, sc = bench.measure(Bc, max(2, min(args.steps, 3)), 3)
             r["config"] = config_dict(name, Bc, 1)
+            capc, _ = load_capture(name, Bc["n_regions"])
+            clkc = (r.get("clocks") or line.get("clocks") or {}).get("sm_mhz")
+            if capc and capc.get("warp_instructions") and clkc:
+                n_sm = torch.cuda.get_device_properties(local_rank).multi_processor_count
+                wi, k_ms_c = capc["warp_instructions"], r["roofline"]["kernel_ms"]
+                r["roofline"]["traffic"] = capc.get("traffic_bytes_per_launch")
+                r["roofline"]["issue_slots"] = {
+                    "warp_instructions_per_launch": wi, "source": f"profiles/{capc['file']} (ncu, this csrc, same workload)",
+                    "frac": wi / (k_ms_c * 1e-3) / (n_sm * 4 * clkc * 1e6)}
             if not args.no_cpu_baseline:
                 r["cpu_baseline"], r["identical_to_reference"] = cpu_baseline_leg(Bc, sc, min_seconds=5.0)
             per[name] = r
