@@ -324,6 +324,18 @@ __device__ __forceinline__ uint32_t first_diff_half(const EditJob& J, int v, int
   const int a = (BITS == 2) ? v : J.P.sh0 + v, b = (BITS == 2) ? h : J.T.sh0 + h;
   const uint32_t* p = J.words + (J.P.word0 + (uint32_t)(a >> Pack<BITS>::kLogBpw));
   const uint32_t* t = J.words + (J.T.word0 + (uint32_t)(b >> Pack<BITS>::kLogBpw));
+#ifdef OTGPU_CHECK_BOUNDS
+  {
+    const CheckRange r0 = otgpu_check_range[0], r1 = otgpu_check_range[1];
+    const bool okp = (p >= r0.lo && p + 2 <= r0.hi) || (p >= r1.lo && p + 2 <= r1.hi);
+    const bool okt = (t >= r0.lo && t + 2 <= r0.hi) || (t >= r1.lo && t + 2 <= r1.hi);
+    if (!okp || !okt) {
+      atomicAdd(&otgpu_check_oob, 1ull);
+      p = t = r0.lo;
+    }
+    if ((threadIdx.x & 31) == 0) atomicAdd(&otgpu_check_loads, 2ull);
+  }
+#endif
   const uint32_t pw = __funnelshift_r(__ldg(p), __ldg(p + 1), a << Pack<BITS>::kLogBits);
   const uint32_t tw = __funnelshift_r(__ldg(t), __ldg(t + 1), b << Pack<BITS>::kLogBits);
   return (uint32_t)(__ffs((pw ^ tw) | 0x80000000u) - 1) >> Pack<BITS>::kLogBits;
